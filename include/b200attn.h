@@ -1,0 +1,156 @@
+/*
+ * b200attn.h — C ABI of the B200-native attention / KV-cache hot path for nano-vllm-x.
+ *
+ * One shared library (libb200attn.so, nvcc -gencode arch=compute_100a,code=sm_100a).  Plain
+ * pointers and sizes only; every pointer is a DEVICE pointer owned by the caller (PyTorch in
+ * the shipped host side) unless the name ends in `_host`.  The library owns no device memory,
+ * never allocates, never synchronises and launches only on the stream it is given, so every
+ * entry point can be captured in a CUDA graph (reference: core/cuda_graph.py:27-39,
+ * core/model_runner.py:407-416).
+ *
+ * Return value: 0 on success, non-zero on error; b200_last_error() then returns a
+ * thread-local message.  Asynchronous faults surface on the caller's next sync, as with the
+ * reference's Triton / FlashInfer launches.
+ *
+ * Citations are into /root/reference/nanovllmx/.
+ */
+#ifndef B200ATTN_H_
+#define B200ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+#define B200ATTN_ABI_VERSION 1
+
+/* dtype codes for K/V/Q/O element type */
+#define B200_DTYPE_BF16 0
+#define B200_DTYPE_FP16 1
+
+int b200_abi_version(void);
+const char* b200_last_error(void);
+/* Number of SMs of the current device (used by the host to size workspaces). <0 on error. */
+int b200_num_sms(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (1) KV slot write.  Replaces the Triton kernel `store_kvcache_kernel` + launcher
+ *     `store_kvcache` (core/kv_cache.py:12-44), called through KVCachePool.set_kv_cache
+ *     (core/kv_cache.py:90-99) from Attention.forward (layers/attention.py:347-352).
+ *
+ *     k, v        : [T, row_elems] rows, element stride 1, row strides k_row_stride /
+ *                   v_row_stride IN ELEMENTS (v is a strided view of the qkv GEMM output,
+ *                   models/qwen3.py:123)
+ *     k_cache,    : [num_slots, row_elems] contiguous layer view of the pool
+ *     v_cache       (core/kv_cache.py:69-79), row_elems = Hkv_local * head_dim
+ *     slots       : [T] int64 (layers/attention.py:134-141); slot < 0 (the reference uses -1,
+ *                   core/kv_cache.py:25-26) => row is skipped
+ *     elem_bytes  : 2 (bf16 / fp16); rows are moved as raw bytes, so the copy is bit-exact
+ * ---------------------------------------------------------------------------------------- */
+int b200_store_kv(const void* k, int64_t k_row_stride, const void* v, int64_t v_row_stride,
+                  void* k_cache, void* v_cache, const int64_t* slots, int32_t T,
+                  int32_t row_elems, int32_t elem_bytes, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (2) Device-side metadata build.  Replaces the torch/host index construction of
+ *     AttentionBackend.build_metadata (layers/attention.py:62-101, 134-141) and
+ *     build_metadata_for_cuda_graph_replay (layers/attention.py:219-275).
+ *
+ *     The worker keeps a device-resident slot table `slot_table[row][col]` (int32): row =
+ *     one live sequence, col = token position, value = KV slot id.  Each step the host
+ *     sends ONE packed int32 message (`step_msg`, already on the device) instead of the
+ *     reference's 2*B per-sequence H2D copies and B `.item()` syncs:
+ *
+ *       step_msg[0*B .. 1*B)  row        slot-table row of sequence i
+ *       step_msg[1*B .. 2*B)  kv_len     len(seq.kv_indices)
+ *       step_msg[2*B .. 3*B)  cached_len seq.cached_kv_len   (new slots = [cached_len, kv_len))
+ *       step_msg[3*B .. 4*B)  q_len      len(seq.token_ids) - seq.cached_kv_len
+ *       step_msg[4*B .. 5*B)  wr_col     first table column written this step
+ *       step_msg[5*B .. 6*B)  wr_cnt     number of slot ids appended to the row this step
+ *       step_msg[6*B .. 7*B)  wr_off     offset of those ids inside the payload
+ *       step_msg[7*B .. 7*B+n_payload)   payload: the new slot ids, int32
+ *
+ *     b200_slot_table_update scatters the payload into the table;
+ *     b200_build_meta then produces, bit-exactly, the arrays the reference builds:
+ *
+ *       qo_indptr       int32 [B+1]           (may be NULL)
+ *       kv_indptr       int32 [padded_bs+1]
+ *       kv_indices      int32 [kv_indices_cap]  first sum(pages) entries = page table
+ *       last_page_len   int32 [padded_bs]     (may be NULL: the graph-replay path of the
+ *                                             reference never rewrites it)
+ *       out_slots       int64 [out_slots_cap]
+ *
+ *     page_size must be a power of two.  For page_size > 1 (not defined by the reference,
+ *     SURVEY.md a-3) pages are page-aligned runs of slots: entry = slot_of_first_token / ps.
+ *
+ *     padded_bs >= B: sequences B..padded_bs-1 are CUDA-graph padding with kv_len 1
+ *     (layers/attention.py:239-244).  If fill_tail != 0 the reference's whole-buffer fills
+ *     are reproduced: kv_indices[sum(pages) .. kv_indices_cap) = 0 (:258) and
+ *     out_slots[sum(new) .. out_slots_cap) = -1 (:265).
+ * ---------------------------------------------------------------------------------------- */
+int b200_slot_table_update(int32_t* slot_table, int64_t table_row_stride, const int32_t* step_msg,
+                           int32_t B, int32_t n_payload, b200_stream_t stream);
+
+int b200_build_meta(const int32_t* slot_table, int64_t table_row_stride, const int32_t* step_msg,
+                    int32_t B, int32_t padded_bs, int32_t page_size, int32_t fill_tail,
+                    int32_t* qo_indptr, int32_t* kv_indptr, int32_t* kv_indices,
+                    int64_t kv_indices_cap, int32_t* last_page_len, int64_t* out_slots,
+                    int64_t out_slots_cap, int32_t* scratch /* >= padded_bs+1 int32 */,
+                    b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (3) Paged GQA decode attention.  Replaces Attention.forward's DECODE branch
+ *     (layers/attention.py:365-369) = FlashInfer BatchDecodeWithPagedKVCacheWrapper.plan+run
+ *     as constructed at layers/attention.py:54-59, 187-207, 277-288.  No host plan: the
+ *     split-KV schedule is computed on the device from kv_indptr, the grid depends only on
+ *     the device (one CTA per SM), so a captured launch stays valid for any batch contents.
+ *
+ *     q, out      : [B, Hq, D], rows q_row_stride / out_row_stride elements apart
+ *     k_cache,    : [num_slots, Hkv, D] layer view (NHD), kv_slot_stride elements between
+ *     v_cache       token slots, D between heads
+ *     kv_indptr   : int32 [B+1]; kv_indices: page ids; last_page_len: int32 [B]
+ *     page_size   : power of two; token t of a sequence lives in slot
+ *                   kv_indices[indptr + t / ps] * ps + t % ps
+ *     workspace   : >= b200_decode_workspace_bytes(B, Hq, Hkv, D) bytes, 16-byte aligned
+ *     Only D == 128 and dtype bf16 are built in round 1.
+ * ---------------------------------------------------------------------------------------- */
+size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D);
+
+int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
+                int64_t kv_slot_stride, const int32_t* kv_indptr, const int32_t* kv_indices,
+                const int32_t* last_page_len, void* out, int64_t out_row_stride, void* workspace,
+                size_t workspace_bytes, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
+                int32_t page_size, float sm_scale, int32_t dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (4) Ragged paged prefill attention (prefix pages + new tokens, bottom-right causal).
+ *     Replaces Attention.forward's PREFILL branch (layers/attention.py:360-364) =
+ *     FlashInfer BatchPrefillWithPagedKVCacheWrapper.plan+run (layers/attention.py:49-53,
+ *     106-119).  Query j of sequence i (Lq new, Lkv total tokens) attends kv positions
+ *     <= Lkv - Lq + j.  K/V of the new tokens must already be in the pool (b200_store_kv).
+ *
+ *     q, out      : [T, Hq, D]; qo_indptr int32 [B+1]; total_q = T (host-known upper bound of
+ *                   qo_indptr[B]; sizes the grid, no device sync)
+ * ---------------------------------------------------------------------------------------- */
+size_t b200_prefill_workspace_bytes(int32_t B, int32_t total_q, int32_t Hq, int32_t Hkv, int32_t D);
+
+int b200_prefill(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
+                 int64_t kv_slot_stride, const int32_t* qo_indptr, const int32_t* kv_indptr,
+                 const int32_t* kv_indices, const int32_t* last_page_len, void* out,
+                 int64_t out_row_stride, void* workspace, size_t workspace_bytes, int32_t B,
+                 int32_t total_q, int32_t Hq, int32_t Hkv, int32_t D, int32_t page_size,
+                 float sm_scale, int32_t causal, int32_t dtype, b200_stream_t stream);
+
+/* Counters for bench.py's `gpu_launches`: number of kernels this library has launched in this
+ * process since load / since the last reset. */
+int64_t b200_launch_count(void);
+void b200_reset_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ATTN_H_ */

@@ -1,0 +1,23 @@
+"""nano-vllm-x_b200 — B200-native attention / KV-cache hot path for nano-vllm-x.
+
+The directory name follows the project layout contract and is not a Python identifier; import it
+with ``importlib.import_module("nano-vllm-x_b200")`` or through the one-line alias module
+``nanovllmx_b200`` at the repo root.  Layout mirrors the two reference files it replaces:
+
+  layers/attention.py  <- nanovllmx/layers/attention.py   (Attention, AttentionBackend, ...)
+  core/kv_cache.py     <- nanovllmx/core/kv_cache.py:12-99 (KVCachePool, store_kvcache)
+  core/cuda_graph.py   <- nanovllmx/core/cuda_graph.py     (graph registry used by the API)
+  ops.py / _lib.py        torch.library ops over the C ABI of include/b200attn.h
+  csrc/                   CUDA kernels for sm_100a + the extern "C" entry points
+"""
+from . import _lib            # noqa: F401
+from . import ops             # noqa: F401  (registers torch.ops.b200attn.*; loads libb200attn.so lazily)
+from .core.common import ForwardBatch, ForwardMode, Sequence       # noqa: F401
+from .core.cuda_graph import CUDAGraph                             # noqa: F401
+from .core.kv_cache import KVCachePool, store_kvcache              # noqa: F401
+from .layers.attention import (Attention, AttentionBackend, AttentionMetadata, AttentionPlan,  # noqa: F401
+                               SlotTable, attention_kv_cache)
+
+__all__ = ["Attention", "AttentionBackend", "AttentionMetadata", "AttentionPlan", "SlotTable",
+           "attention_kv_cache", "KVCachePool", "store_kvcache", "CUDAGraph", "ForwardBatch", "ForwardMode",
+           "Sequence", "ops"]

@@ -1,0 +1,419 @@
+// (3) Paged GQA decode attention for sm_100a — split-KV streaming kernel + merge pass.
+// Replaces layers/attention.py:365-369 (FlashInfer BatchDecodeWithPagedKVCacheWrapper, CUDA-core
+// cp.async kernel decode.cuh:613 + host plan()).  Own design, not a port:
+//
+//  * Schedule on the device, balanced by construction.  All sequences' KV is viewed as one
+//    flat list of 16-token tiles; the grid is ONE CTA PER SM and CTA c owns the contiguous
+//    tile range [c*per, (c+1)*per).  A CTA's range may cover the tail of one sequence and the
+//    head of the next; every (CTA, sequence) intersection is a "segment" that yields one
+//    partial (o, lse).  No host plan, no sync, grid independent of the batch => graph-safe.
+//  * One warp = one KV head (all `group` query heads that share it form the M rows of the
+//    mma tile), so K/V are read from HBM exactly once per KV head, and the 8 warps of a CTA
+//    walk the SAME tokens of 8 different heads => a CTA reads whole contiguous token rows
+//    (page_size 1: 2 x Hkv*256 B per token; page_size 16: whole 32 KiB pages).
+//    With fewer than 8 KV heads per rank (TP 2/4/8) the spare warps split the tile range.
+//  * Each warp runs a private 3-stage cp.async (LDGSTS, 16 B, L1-bypass) pipeline into
+//    XOR-swizzled shared memory: no __syncthreads in the steady state, ~190 KiB in flight per SM.
+//  * q.K^T and p.V use mma.sync m16n8k16 (bf16 in, fp32 accumulate) fed by ldmatrix; decode is
+//    HBM-bound, tensor throughput is irrelevant here, the point is ~10x fewer issue slots than
+//    an FMA formulation.  Online softmax in fp32 with quad shuffles (exp2 domain).
+//  * Segments that cover a whole sequence write bf16 output directly; the rest write fp32
+//    partials + log-sum-exp to the workspace and a small merge kernel combines them.
+//
+// Algorithmic bytes per call: sum_i 2*Lkv_i*Hkv*D*2 + 2*B*Hq*D*2 + index bytes.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kD = 128;             // head dim built in round 1
+constexpr int kTile = 16;           // tokens per pipeline tile
+constexpr int kWarps = 8;           // warps per CTA
+constexpr int kStages = 3;          // cp.async stages per warp
+constexpr int kRowBytes = kD * 2;   // 256 B per (token, head) row
+constexpr int kTileBytes = kTile * kRowBytes;          // 4 KiB (K or V)
+constexpr int kStageBytes = 2 * kTileBytes;            // K + V
+constexpr int kWarpSmem = kStages * kStageBytes;       // 24 KiB
+constexpr int kDecodeSmem = kWarps * kWarpSmem;        // 192 KiB
+constexpr int kMinTilesPerCta = 8;  // do not split finer than 128 tokens per CTA
+
+struct DecodeParams {
+  const __nv_bfloat16* q;
+  const __nv_bfloat16* k_cache;
+  const __nv_bfloat16* v_cache;
+  const int32_t* kv_indptr;
+  const int32_t* kv_indices;
+  const int32_t* last_page_len;
+  __nv_bfloat16* out;
+  float* part_o;      // [(G+B)*S][Hq][D]
+  float* part_lse;    // [(G+B)*S][Hq]
+  int32_t* seg_first; // [B]
+  int32_t* seg_last;  // [B]
+  int64_t q_row_stride, out_row_stride, kv_slot_stride;
+  int B, Hq, Hkv, group, log2_ps;
+  int heads_per_cta;  // KV heads handled by one CTA (<= 8)
+  int subs;           // warps per KV head (tile-range split inside the CTA)
+  float scale_log2;   // sm_scale * log2(e)
+};
+
+__device__ __forceinline__ int tiles_of(const DecodeParams& p, int i) {
+  return (seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps) + kTile - 1) / kTile;
+}
+
+__global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodeParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ int s_scan[kWarps + 1];
+  __shared__ int s_loc[2];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = gridDim.x;
+  const int head_group = blockIdx.y;  // which block of heads_per_cta KV heads
+
+  // ---- device-side schedule: total tiles, this CTA's range, first sequence ------------------
+  int total;
+  {
+    int local = 0;
+    for (int i = tid; i < p.B; i += kWarps * 32) local += tiles_of(p, i);
+    (void)block_inclusive_scan<kWarps * 32>(local, s_scan, &total);
+  }
+  int per = (total + G - 1) / G;
+  if (per < kMinTilesPerCta) per = kMinTilesPerCta;
+  const int t_begin = blockIdx.x * per;
+  if (t_begin >= total) return;
+  const int t_end = min(t_begin + per, total);
+  {
+    int carry = 0;
+    for (int base = 0; base < p.B; base += kWarps * 32) {
+      const int i = base + tid;
+      const int t = i < p.B ? tiles_of(p, i) : 0;
+      int blk;
+      const int incl = block_inclusive_scan<kWarps * 32>(t, s_scan, &blk) + carry;
+      const int excl = incl - t;
+      if (t > 0 && excl <= t_begin && t_begin < incl) {
+        s_loc[0] = i;
+        s_loc[1] = excl;
+      }
+      carry += blk;
+      if (carry > t_begin) break;
+    }
+    __syncthreads();
+  }
+
+  const int hh = warp % p.heads_per_cta;           // KV head inside the CTA's head block
+  const int sub = warp / p.heads_per_cta;          // which slice of the tile range
+  const bool warp_active = sub < p.subs;
+  const int kv_head = head_group * p.heads_per_cta + hh;
+  const int row = lane >> 2;                        // mma row = query head inside the group
+  const int quad = lane & 3;
+  const bool row_real = row < p.group;
+  const uint32_t warp_smem = smem_u32(smem) + warp * kWarpSmem;
+
+  // per-lane constants of the loaders
+  const int ld_chunk = lane & 15;                   // 16-byte chunk inside the 256-byte row
+  const int ld_rsel = lane >> 4;                    // rows 2i + ld_rsel
+  const __nv_bfloat16* kbase = p.k_cache + (int64_t)kv_head * kD + ld_chunk * 8;
+  const __nv_bfloat16* vbase = p.v_cache + (int64_t)kv_head * kD + ld_chunk * 8;
+  const int ps_mask = (1 << p.log2_ps) - 1;
+
+  // ldmatrix lane addresses (byte offsets inside a 4 KiB tile, before the per-step chunk xor)
+  //   K (non-trans): matrix m = lane/8: token = (m>>1)*8 + lane%8, chunk = 2*ks + (m&1)
+  //   V (trans)    : token = (m&1)*8 + lane%8,  chunk = 2*j + (m>>1)
+  const int lm = lane >> 3, lr = lane & 7;
+  const int k_tok = (lm >> 1) * 8 + lr, k_csel = lm & 1;
+  const int v_tok = (lm & 1) * 8 + lr, v_csel = lm >> 1;
+
+  int s = s_loc[0];
+  int pre = s_loc[1];
+  int t = t_begin;
+  while (t < t_end) {
+    const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
+    const int nt = (L + kTile - 1) / kTile;
+    if (nt == 0) {
+      ++s;
+      continue;
+    }
+    const int seg_b = t - pre;
+    const int seg_e = min(t_end, pre + nt) - pre;
+    const int slot_id = blockIdx.x + s;  // unique per (CTA, sequence) segment, see header
+    const bool whole = (seg_b == 0) && (seg_e == nt);
+    if (tid == 0 && head_group == 0) {
+      if (seg_b == 0) p.seg_first[s] = slot_id;
+      if (seg_e == nt) p.seg_last[s] = slot_id;
+    }
+
+    if (warp_active) {
+      const int page0 = p.kv_indptr[s];
+      // ---- Q fragments (A operand, 16 x 128): rows >= group are zero ------------------------
+      uint32_t qa[kD / 16][4];
+      {
+        const __nv_bfloat16* qrow = p.q + (int64_t)s * p.q_row_stride + (int64_t)(kv_head * p.group + row) * kD;
+#pragma unroll
+        for (int ks = 0; ks < kD / 16; ++ks) {
+          uint32_t lo = 0, hi = 0;
+          if (row_real) {
+            lo = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + quad * 2);
+            hi = *reinterpret_cast<const uint32_t*>(qrow + ks * 16 + 8 + quad * 2);
+          }
+          qa[ks][0] = lo; qa[ks][1] = 0u; qa[ks][2] = hi; qa[ks][3] = 0u;
+        }
+      }
+      float o[kD / 8][2];
+#pragma unroll
+      for (int j = 0; j < kD / 8; ++j) o[j][0] = o[j][1] = 0.f;
+      float m_run = -INFINITY, l_run = 0.f;
+
+      // my tiles: seg_b + sub, seg_b + sub + subs, ...
+      const int n_my = (seg_e - seg_b - sub + p.subs - 1) / p.subs;  // may be <= 0
+      auto tile_of = [&](int it) { return seg_b + sub + it * p.subs; };
+
+      // slot id of row (lane & 15) of a tile, fetched one tile ahead of its use
+      auto fetch_slot = [&](int tile) -> int {
+        const int tok = tile * kTile + (lane & 15);
+        if (tok >= L) return -1;
+        const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
+        return (page << p.log2_ps) + (tok & ps_mask);
+      };
+      auto issue = [&](int it, int my_slot) {
+        const uint32_t st = warp_smem + (it % kStages) * kStageBytes;
+#pragma unroll
+        for (int i = 0; i < kTile / 2; ++i) {
+          const int r = 2 * i + ld_rsel;
+          const int slot = __shfl_sync(0xffffffffu, my_slot, r);
+          const bool ok = slot >= 0;
+          const int64_t off = ok ? (int64_t)slot * p.kv_slot_stride : 0;
+          const uint32_t dst = st + r * kRowBytes + ((ld_chunk ^ (r & 7)) << 4);
+          cp_async_16(dst, kbase + off, ok ? 16u : 0u);
+          cp_async_16(dst + kTileBytes, vbase + off, ok ? 16u : 0u);
+        }
+      };
+
+      int next_slot = n_my > 0 ? fetch_slot(tile_of(0)) : -1;
+#pragma unroll
+      for (int it = 0; it < kStages - 1; ++it) {
+        if (it < n_my) {
+          const int cur = next_slot;
+          next_slot = (it + 1 < n_my) ? fetch_slot(tile_of(it + 1)) : -1;
+          issue(it, cur);
+        }
+        cp_async_commit();
+      }
+
+      for (int it = 0; it < n_my; ++it) {
+        {
+          const int nx = it + kStages - 1;
+          if (nx < n_my) {
+            const int cur = next_slot;
+            next_slot = (nx + 1 < n_my) ? fetch_slot(tile_of(nx + 1)) : -1;
+            issue(nx, cur);
+          }
+          cp_async_commit();
+        }
+        cp_async_wait<kStages - 1>();
+        __syncwarp();
+
+        const uint32_t kst = warp_smem + (it % kStages) * kStageBytes;
+        const uint32_t vst = kst + kTileBytes;
+        const int tile = tile_of(it);
+
+        // ---- S = Q K^T (16 x 16 tokens) -------------------------------------------------------
+        float sc[2][4];
+#pragma unroll
+        for (int n = 0; n < 2; ++n) sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < kD / 16; ++ks) {
+          uint32_t b[4];
+          ldmatrix_x4(b, kst + k_tok * kRowBytes + (((2 * ks + k_csel) ^ (k_tok & 7)) << 4));
+          mma_bf16_16816(sc[0], qa[ks], b[0], b[1]);
+          mma_bf16_16816(sc[1], qa[ks], b[2], b[3]);
+        }
+        // ---- online softmax on row `row`, columns tok0 + {0,1,8,9} ---------------------------
+        const int tok0 = tile * kTile + quad * 2;
+        float x0 = sc[0][0] * p.scale_log2, x1 = sc[0][1] * p.scale_log2;
+        float x2 = sc[1][0] * p.scale_log2, x3 = sc[1][1] * p.scale_log2;
+        if (tile * kTile + kTile > L) {
+          if (tok0 >= L) x0 = -INFINITY;
+          if (tok0 + 1 >= L) x1 = -INFINITY;
+          if (tok0 + 8 >= L) x2 = -INFINITY;
+          if (tok0 + 9 >= L) x3 = -INFINITY;
+        }
+        float mx = fmaxf(fmaxf(x0, x1), fmaxf(x2, x3));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float m_new = fmaxf(m_run, mx);  // finite: every tile holds >= 1 valid token
+        const float alpha = fast_exp2(m_run - m_new);
+        const float p0 = fast_exp2(x0 - m_new), p1 = fast_exp2(x1 - m_new);
+        const float p2 = fast_exp2(x2 - m_new), p3 = fast_exp2(x3 - m_new);
+        l_run = l_run * alpha + (p0 + p1) + (p2 + p3);
+        if (__any_sync(0xffffffffu, m_new != m_run)) {
+#pragma unroll
+          for (int j = 0; j < kD / 8; ++j) {
+            o[j][0] *= alpha;
+            o[j][1] *= alpha;
+          }
+        }
+        m_run = m_new;
+        uint32_t pa[4];
+        pa[0] = pack_bf16x2(p0, p1); pa[1] = 0u; pa[2] = pack_bf16x2(p2, p3); pa[3] = 0u;
+        // ---- O += P V ---------------------------------------------------------------------------
+#pragma unroll
+        for (int j = 0; j < kD / 16; ++j) {
+          uint32_t b[4];
+          ldmatrix_x4_trans(b, vst + v_tok * kRowBytes + (((2 * j + v_csel) ^ (v_tok & 7)) << 4));
+          float c0[4] = {o[2 * j][0], o[2 * j][1], 0.f, 0.f};
+          float c1[4] = {o[2 * j + 1][0], o[2 * j + 1][1], 0.f, 0.f};
+          mma_bf16_16816(c0, pa, b[0], b[1]);
+          mma_bf16_16816(c1, pa, b[2], b[3]);
+          o[2 * j][0] = c0[0]; o[2 * j][1] = c0[1];
+          o[2 * j + 1][0] = c1[0]; o[2 * j + 1][1] = c1[1];
+        }
+        __syncwarp();
+      }
+      cp_async_wait<0>();
+
+      // ---- segment epilogue ----------------------------------------------------------------------
+      l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+      l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+      if (row_real) {
+        const int hq = kv_head * p.group + row;
+        if (whole && p.subs == 1) {
+          __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD + quad * 2;
+#pragma unroll
+          for (int j = 0; j < kD / 8; ++j)
+            *reinterpret_cast<uint32_t*>(dst + j * 8) = pack_bf16x2(o[j][0] * inv_l, o[j][1] * inv_l);
+        } else {
+          const int64_t pidx = (int64_t)slot_id * p.subs + sub;
+          float* dst = p.part_o + (pidx * p.Hq + hq) * kD + quad * 2;
+#pragma unroll
+          for (int j = 0; j < kD / 8; ++j)
+            *reinterpret_cast<float2*>(dst + j * 8) = make_float2(o[j][0] * inv_l, o[j][1] * inv_l);
+          if (quad == 0) p.part_lse[pidx * p.Hq + hq] = l_run > 0.f ? m_run + fast_log2(l_run) : -INFINITY;
+        }
+      }
+    }
+    t = pre + seg_e;
+    pre += nt;
+    ++s;
+  }
+}
+
+// Merge pass: one CTA per (sequence, query head), one thread per output dim.
+__global__ void __launch_bounds__(kD) decode_merge_kernel(const DecodeParams p) {
+  const int s = blockIdx.x, hq = blockIdx.y, d = threadIdx.x;
+  __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD + d;
+  const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
+  if (L == 0) {
+    *dst = __float2bfloat16(0.f);
+    return;
+  }
+  const int first = p.seg_first[s], last = p.seg_last[s];
+  if (p.subs == 1 && first == last) return;  // written directly by the streaming kernel
+  const int64_t p0 = (int64_t)first * p.subs;
+  const int n = (last - first + 1) * p.subs;
+  float mx = -INFINITY;
+  for (int i = 0; i < n; ++i) mx = fmaxf(mx, p.part_lse[(p0 + i) * p.Hq + hq]);
+  float acc = 0.f, wsum = 0.f;
+  for (int i = 0; i < n; ++i) {
+    const float lse = p.part_lse[(p0 + i) * p.Hq + hq];
+    if (lse == -INFINITY) continue;
+    const float w = fast_exp2(lse - mx);
+    wsum += w;
+    acc += w * p.part_o[((p0 + i) * p.Hq + hq) * kD + d];
+  }
+  *dst = __float2bfloat16(wsum > 0.f ? acc / wsum : 0.f);
+}
+
+static int ilog2_exact_d(int x) {
+  if (x <= 0 || (x & (x - 1))) return -1;
+  int l = 0;
+  while ((1 << l) < x) ++l;
+  return l;
+}
+
+struct DecodeCfg {
+  int heads_per_cta, subs, head_groups;
+};
+static bool decode_cfg(int Hkv, DecodeCfg* c) {
+  if (Hkv <= 0) return false;
+  if (Hkv >= kWarps) {
+    if (Hkv % kWarps) return false;
+    *c = {kWarps, 1, Hkv / kWarps};
+  } else {
+    *c = {Hkv, kWarps / Hkv, 1};  // Hkv in 1..7: subs = floor(8/Hkv) warps per head
+  }
+  return true;
+}
+
+}  // namespace b200
+
+extern "C" size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D) {
+  using namespace b200;
+  DecodeCfg c;
+  if (B <= 0 || Hq <= 0 || D <= 0 || !decode_cfg(Hkv, &c)) return 0;
+  const int G = cached_num_sms();
+  const size_t parts = (size_t)(G + B) * c.subs;
+  size_t bytes = parts * Hq * D * sizeof(float);       // part_o
+  bytes += parts * Hq * sizeof(float);                 // part_lse
+  bytes += 2 * (size_t)B * sizeof(int32_t);            // seg_first / seg_last
+  return (bytes + 255) & ~(size_t)255;
+}
+
+extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
+                           int64_t kv_slot_stride, const int32_t* kv_indptr, const int32_t* kv_indices,
+                           const int32_t* last_page_len, void* out, int64_t out_row_stride, void* workspace,
+                           size_t workspace_bytes, int32_t B, int32_t Hq, int32_t Hkv, int32_t D, int32_t page_size,
+                           float sm_scale, int32_t dtype, b200_stream_t stream) {
+  using namespace b200;
+  if (B < 0) return fail("b200_decode: B < 0");
+  if (B == 0) return 0;
+  if (D != kD) return fail("b200_decode: head_dim %d not built (round 1 builds D=128)", D);
+  if (dtype != B200_DTYPE_BF16) return fail("b200_decode: dtype %d not built (bf16 only)", dtype);
+  DecodeCfg c;
+  if (!decode_cfg(Hkv, &c)) return fail("b200_decode: unsupported num_kv_heads %d", Hkv);
+  if (Hq % Hkv) return fail("b200_decode: Hq %d not a multiple of Hkv %d", Hq, Hkv);
+  const int group = Hq / Hkv;
+  if (group > 8) return fail("b200_decode: GQA group %d > 8 not built", group);
+  const int log2_ps = ilog2_exact_d(page_size);
+  if (log2_ps < 0) return fail("b200_decode: page_size %d is not a power of two", page_size);
+  if (!q || !k_cache || !v_cache || !kv_indptr || !kv_indices || !last_page_len || !out || !workspace)
+    return fail("b200_decode: null pointer");
+  if (((uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)workspace) & 15 || (kv_slot_stride & 7))
+    return fail("b200_decode: k_cache / v_cache / workspace must be 16-byte aligned");
+  if (((uintptr_t)q | (uintptr_t)out) & 3 || (q_row_stride & 1) || (out_row_stride & 1))
+    return fail("b200_decode: q / out must be 4-byte aligned");
+  const size_t need = b200_decode_workspace_bytes(B, Hq, Hkv, D);
+  if (workspace_bytes < need) return fail("b200_decode: workspace %zu < %zu bytes", workspace_bytes, need);
+
+  const int G = cached_num_sms();
+  DecodeParams p;
+  p.q = (const __nv_bfloat16*)q;
+  p.k_cache = (const __nv_bfloat16*)k_cache;
+  p.v_cache = (const __nv_bfloat16*)v_cache;
+  p.kv_indptr = kv_indptr;
+  p.kv_indices = kv_indices;
+  p.last_page_len = last_page_len;
+  p.out = (__nv_bfloat16*)out;
+  const size_t parts = (size_t)(G + B) * c.subs;
+  p.part_o = (float*)workspace;
+  p.part_lse = p.part_o + parts * Hq * D;
+  p.seg_first = (int32_t*)(p.part_lse + parts * Hq);
+  p.seg_last = p.seg_first + B;
+  p.q_row_stride = q_row_stride;
+  p.out_row_stride = out_row_stride;
+  p.kv_slot_stride = kv_slot_stride;
+  p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.group = group; p.log2_ps = log2_ps;
+  p.heads_per_cta = c.heads_per_cta;
+  p.subs = c.subs;
+  p.scale_log2 = sm_scale * kLog2e;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDecodeSmem);
+    if (e != cudaSuccess) return fail("b200_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
+  if (int rc = check_launch("b200_decode(stream)")) return rc;
+  decode_merge_kernel<<<dim3(B, Hq), kD, 0, st>>>(p);
+  return check_launch("b200_decode(merge)");
+}

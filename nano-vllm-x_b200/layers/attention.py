@@ -1,0 +1,378 @@
+"""Drop-in replacement for nanovllmx/layers/attention.py (reference :17-373).
+
+Same public surface — ``AttentionMetadata``, ``AttentionBackend`` (``build_metadata``,
+``prepare_for_cuda_graph_capture``, ``build_metadata_for_cuda_graph_capture``,
+``build_metadata_for_cuda_graph_replay``), ``attention_kv_cache``, ``Attention`` — and the same
+named CUDA-graph buffers (``paged_kv_indptr_buffer``, ``paged_kv_indices_buffer``,
+``paged_kv_last_page_len_buffer``, ``output_kv_indices_buffer``; reference :158-168) with
+bit-identical contents.  What changes underneath:
+
+* no FlashInfer, no Triton, no host ``plan()``: the ``wrapper`` field of the metadata holds an
+  ``AttentionPlan`` (device index arrays + workspace) consumed by the b200attn CUDA kernels;
+* the index arrays are built ON THE DEVICE from a device-resident slot table.  Per step the host
+  sends one packed int32 message (rows, lengths and only the NEW slot ids) instead of the
+  reference's 2*B list->tensor H2D copies, B ``.item()`` syncs (reference :92-101) and O(sum L)
+  Python list traversal;
+* nothing in this file synchronises with the device.
+"""
+from __future__ import annotations
+
+import os
+from contextlib import contextmanager
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..core.common import mode_name
+from ..core.kv_cache import KVCachePool
+
+
+# =======================================================================================================
+# plan object stored in AttentionMetadata.wrapper
+# =======================================================================================================
+class AttentionPlan:
+    """What FlashInfer's wrapper object is to the reference (:49-59): the per-step state the
+    attention kernels read.  All arrays live on the device; ``total_q`` / ``num_seqs`` are host
+    ints known without a sync."""
+
+    def __init__(self, mode: str, num_seqs: int, total_q: int, page_size: int,
+                 qo_indptr: Optional[torch.Tensor], paged_kv_indptr: torch.Tensor,
+                 paged_kv_indices: torch.Tensor, paged_kv_last_page_len: torch.Tensor,
+                 workspace: torch.Tensor, num_qo_heads: int, num_kv_heads: int, head_dim: int):
+        self.mode = mode
+        self.num_seqs = num_seqs
+        self.total_q = total_q
+        self.page_size = page_size
+        self.qo_indptr = qo_indptr
+        self.paged_kv_indptr = paged_kv_indptr
+        self.paged_kv_indices = paged_kv_indices
+        self.paged_kv_last_page_len = paged_kv_last_page_len
+        self.workspace = workspace
+        self.num_qo_heads = num_qo_heads
+        self.num_kv_heads = num_kv_heads
+        self.head_dim = head_dim
+        self._sm_scale = head_dim ** -0.5   # overwritten by Attention.forward, as the reference does (:361,:366)
+
+    def run(self, q: torch.Tensor, paged_kv_cache) -> torch.Tensor:
+        """q: [T, Hq, D]; paged_kv_cache = (k_cache, v_cache), each [num_tokens, 1, Hkv, D] or
+        [num_tokens, Hkv, D].  Returns [T, Hq, D] (same call shape as FlashInfer's ``run``)."""
+        k_cache, v_cache = paged_kv_cache
+        k_cache = k_cache.view(-1, self.num_kv_heads, self.head_dim)
+        v_cache = v_cache.view(-1, self.num_kv_heads, self.head_dim)
+        if self.mode == "DECODE":
+            return ops.decode(q, k_cache, v_cache, self.paged_kv_indptr, self.paged_kv_indices,
+                              self.paged_kv_last_page_len, self.workspace, self.page_size, self._sm_scale)
+        return ops.prefill(q, k_cache, v_cache, self.qo_indptr, self.paged_kv_indptr, self.paged_kv_indices,
+                           self.paged_kv_last_page_len, self.workspace, self.page_size, self._sm_scale, True)
+
+
+@dataclass
+class AttentionMetadata:
+    forward_mode: object            # ForwardMode (reference's or ours)
+    kv_cache: KVCachePool
+    output_kv_indices: torch.Tensor
+    wrapper: AttentionPlan
+
+
+# =======================================================================================================
+# device-resident slot table
+# =======================================================================================================
+class SlotTable:
+    """``table[row, pos]`` = KV slot id of token ``pos`` of the live sequence in ``row``.
+
+    Workers receive freshly pickled ``Sequence`` objects every step (reference
+    core/executor.py:94-95), so rows are keyed by ``seq_id``.  Contract used for the delta
+    upload: positions ``< seq.cached_kv_len`` were computed in an earlier step and, if this
+    sequence's row already holds at least that many entries, are unchanged; everything from
+    ``min(tracked, cached_kv_len)`` on is (re)sent.  A preempted sequence comes back with
+    ``cached_kv_len == 0`` (core/scheduler.py:130-138) and is therefore resent in full, as is any
+    unknown ``seq_id``.  ``B200ATTN_VERIFY=1`` keeps a host mirror and checks the contract every
+    step (debug aid; O(sum L) like the reference).
+    """
+
+    def __init__(self, device: torch.device, rows: int = 64, cols: int = 1024):
+        self.device = device
+        self.table = torch.zeros((rows, cols), dtype=torch.int32, device=device)
+        self.row_of: dict = {}
+        self.tracked_len: list[int] = [0] * rows
+        self.last_used: list[int] = [0] * rows
+        self.owner: list = [None] * rows
+        self.free_rows = list(range(rows - 1, -1, -1))
+        self.step = 0
+        self.verify = os.environ.get("B200ATTN_VERIFY", "0") == "1"
+        self._mirror: dict = {}
+
+    # -- capacity ----------------------------------------------------------------------------------
+    def _grow(self, rows: int, cols: int) -> None:
+        old = self.table
+        rows = max(rows, old.shape[0])
+        cols = max(cols, old.shape[1])
+        if rows == old.shape[0] and cols == old.shape[1]:
+            return
+        new = torch.zeros((rows, cols), dtype=torch.int32, device=self.device)
+        new[:old.shape[0], :old.shape[1]].copy_(old)
+        self.table = new
+        extra = rows - old.shape[0]
+        if extra > 0:
+            self.free_rows = list(range(rows - 1, old.shape[0] - 1, -1)) + self.free_rows
+            self.tracked_len += [0] * extra
+            self.last_used += [0] * extra
+            self.owner += [None] * extra
+
+    def reserve(self, rows: int, cols: int) -> None:
+        self._grow(rows, cols)
+
+    def _take_row(self, need_now: int) -> int:
+        if not self.free_rows:
+            # evict rows that are not part of the current step, oldest first
+            stale = [r for r in range(len(self.owner)) if self.last_used[r] != self.step and self.owner[r] is not None]
+            if len(stale) < need_now:
+                self._grow(max(2 * self.table.shape[0], self.table.shape[0] + need_now), self.table.shape[1])
+            else:
+                stale.sort(key=lambda r: self.last_used[r])
+                for r in stale[:max(need_now, len(stale) // 2)]:
+                    self.row_of.pop(self.owner[r], None)
+                    self._mirror.pop(self.owner[r], None)
+                    self.owner[r] = None
+                    self.tracked_len[r] = 0
+                    self.free_rows.append(r)
+        return self.free_rows.pop()
+
+    # -- per step ----------------------------------------------------------------------------------
+    def pack_step(self, seqs) -> tuple[torch.Tensor, int, int, int, int]:
+        """Returns (device message, n_payload, total_q, total_pages_at_ps1, total_new)."""
+        self.step += 1
+        B = len(seqs)
+        max_len = 0
+        for s in seqs:
+            n = len(s.kv_indices)
+            if n > max_len:
+                max_len = n
+        if max_len > self.table.shape[1]:
+            self._grow(self.table.shape[0], max(max_len, 2 * self.table.shape[1]))
+        hdr = np.empty((7, B), dtype=np.int32)
+        payload: list = []
+        total_q = total_kv = total_new = 0
+        unknown = sum(1 for s in seqs if s.seq_id not in self.row_of)
+        for i, s in enumerate(seqs):
+            kv = s.kv_indices
+            n = len(kv)
+            cached = s.cached_kv_len
+            row = self.row_of.get(s.seq_id)
+            if row is None:
+                row = self._take_row(unknown)
+                self.row_of[s.seq_id] = row
+                self.owner[row] = s.seq_id
+                start = 0
+            else:
+                start = min(self.tracked_len[row], cached)
+            if self.verify:
+                mir = self._mirror.get(s.seq_id, [])
+                assert mir[:start] == list(kv[:start]), f"slot table contract violated for seq {s.seq_id}"
+                self._mirror[s.seq_id] = list(kv)
+            self.last_used[row] = self.step
+            cnt = n - start if n > start else 0
+            hdr[0, i] = row
+            hdr[1, i] = n
+            hdr[2, i] = cached
+            q = len(s.token_ids) - cached
+            hdr[3, i] = q
+            hdr[4, i] = start
+            hdr[5, i] = cnt
+            hdr[6, i] = len(payload)
+            if cnt:
+                payload.extend(kv[start:] if start else kv)
+            self.tracked_len[row] = n
+            total_q += q
+            total_kv += n
+            total_new += n - cached if n > cached else 0
+        msg = np.empty(7 * B + len(payload), dtype=np.int32)
+        msg[:7 * B] = hdr.reshape(-1)
+        if payload:
+            msg[7 * B:] = payload
+        host = torch.from_numpy(msg)
+        if self.device.type == "cuda":
+            host = host.pin_memory()
+        dev = host.to(self.device, non_blocking=True)
+        self.last_msg_bytes = msg.nbytes
+        return dev, len(payload), total_q, total_kv, total_new
+
+
+# =======================================================================================================
+# backend
+# =======================================================================================================
+class AttentionBackend:
+    """Signature of the reference constructor (:26-34); ``page_size`` is an extension (the
+    reference hard-codes 1, :66) used by the long-context page-16 configuration."""
+
+    def __init__(self, kv_cache: KVCachePool, num_qo_heads: int, num_kv_heads: int, head_dim: int,
+                 dtype: torch.dtype, device: torch.device, page_size: int = 1):
+        self.kv_cache = kv_cache
+        self.num_qo_heads = num_qo_heads
+        self.num_kv_heads = num_kv_heads
+        self.head_dim = head_dim
+        self.dtype = dtype
+        self.device = torch.device(device)
+        self.page_size = page_size
+        assert page_size >= 1 and (page_size & (page_size - 1)) == 0, "page_size must be a power of two"
+        if self.device.type != "cuda":
+            raise RuntimeError("AttentionBackend needs a CUDA device: the b200attn path has no CPU fallback")
+        self.slot_table = SlotTable(self.device)
+        self._workspace = torch.empty(0, dtype=torch.uint8, device=self.device)
+        self._graph_plans: dict[int, AttentionPlan] = {}
+        self._graph_scratch: Optional[torch.Tensor] = None
+
+    # -- helpers -----------------------------------------------------------------------------------
+    def _ensure_workspace(self, bs: int, total_q: int) -> torch.Tensor:
+        need = max(ops.decode_workspace_bytes(max(bs, 1), self.num_qo_heads, self.num_kv_heads, self.head_dim),
+                   ops.prefill_workspace_bytes(max(bs, 1), max(total_q, 1), self.num_qo_heads, self.num_kv_heads,
+                                               self.head_dim))
+        if self._workspace.numel() < need:
+            # plans captured in CUDA graphs keep a reference to the buffer they were captured with
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._workspace
+
+    def _pages(self, n_tokens_total_upper: int, B: int) -> int:
+        ps = self.page_size
+        return n_tokens_total_upper if ps == 1 else (n_tokens_total_upper + ps - 1) // ps + B
+
+    # -- eager ---------------------------------------------------------------------------------------
+    def build_metadata(self, batch) -> AttentionMetadata:
+        """Reference :62-149.  Produces the same arrays (bit-exact at page_size 1)."""
+        seqs = batch.seqs
+        B = len(seqs)
+        mode = mode_name(batch.forward_mode)
+        st = self.slot_table
+        msg, n_payload, total_q, total_kv, total_new = st.pack_step(seqs)
+        ops.slot_table_update(st.table, msg, B, n_payload)
+        ps = self.page_size
+        if ps == 1:
+            n_pages = total_kv
+        else:
+            n_pages = sum((len(s.kv_indices) + ps - 1) // ps for s in seqs)
+        dev = self.device
+        qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        kv_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        kv_indices = torch.empty(n_pages, dtype=torch.int32, device=dev)
+        last_page_len = torch.empty(B, dtype=torch.int32, device=dev)
+        out_slots = torch.empty(total_new, dtype=torch.int64, device=dev)
+        scratch = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        if B > 0:
+            ops.build_meta(st.table, msg, B, B, ps, False, qo_indptr, kv_indptr, kv_indices, last_page_len,
+                           out_slots, scratch)
+        else:
+            qo_indptr.zero_()
+            kv_indptr.zero_()
+        plan = AttentionPlan(mode, B, total_q, ps, qo_indptr, kv_indptr, kv_indices, last_page_len,
+                             self._ensure_workspace(B, total_q), self.num_qo_heads, self.num_kv_heads,
+                             self.head_dim)
+        return AttentionMetadata(forward_mode=batch.forward_mode, kv_cache=self.kv_cache,
+                                 output_kv_indices=out_slots, wrapper=plan)
+
+    # -- CUDA graphs -----------------------------------------------------------------------------------
+    def prepare_for_cuda_graph_capture(self, graph, max_bs: int, context_len: int) -> None:
+        """Reference :151-168: same four named buffers, same dtypes, shapes and initial contents."""
+        dev = self.device
+        graph.set_input_buffer("paged_kv_indptr_buffer",
+                               torch.arange(0, max_bs + 1, dtype=torch.int32, device=dev) * context_len)
+        graph.set_input_buffer("paged_kv_indices_buffer",
+                               torch.zeros((max_bs * context_len,), dtype=torch.int32, device=dev))
+        graph.set_input_buffer("paged_kv_last_page_len_buffer",
+                               torch.ones((max_bs,), dtype=torch.int32, device=dev))
+        graph.set_input_buffer("output_kv_indices_buffer",
+                               torch.zeros((max_bs,), dtype=torch.int64, device=dev))
+        self._graph_scratch = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)
+        self.slot_table.reserve(2 * max_bs, context_len)
+        # one workspace, sized for the largest captured batch, shared by all graphs
+        self._graph_workspace = torch.empty(
+            ops.decode_workspace_bytes(max_bs, self.num_qo_heads, self.num_kv_heads, self.head_dim),
+            dtype=torch.uint8, device=dev)
+        self._graph_context_len = context_len
+
+    def build_metadata_for_cuda_graph_capture(self, graph, bs: int, context_len: int) -> AttentionMetadata:
+        """Reference :171-216: metadata over slices of the static buffers (worst case: every
+        sequence ``context_len`` long, which is what the initial indptr encodes)."""
+        indptr = graph.get_input_buffer("paged_kv_indptr_buffer")[:bs + 1]
+        indices = graph.get_input_buffer("paged_kv_indices_buffer")[:bs * context_len]
+        last = graph.get_input_buffer("paged_kv_last_page_len_buffer")[:bs]
+        out_idx = graph.get_input_buffer("output_kv_indices_buffer")[:bs]
+        from ..core.common import ForwardMode
+        plan = AttentionPlan("DECODE", bs, bs, self.page_size, None, indptr, indices, last,
+                             self._graph_workspace, self.num_qo_heads, self.num_kv_heads, self.head_dim)
+        self._graph_plans[bs] = plan
+        return AttentionMetadata(forward_mode=ForwardMode.DECODE, kv_cache=self.kv_cache,
+                                 output_kv_indices=out_idx, wrapper=plan)
+
+    def build_metadata_for_cuda_graph_replay(self, graph, batch, padded_bs: int) -> AttentionMetadata:
+        """Reference :219-295: refill the static buffers for this step (padding sequences have
+        kv_len 1 -> slot 0, slot map -1), with two kernels instead of 2*B copies + a host plan."""
+        seqs = batch.seqs
+        bs = len(seqs)
+        st = self.slot_table
+        msg, n_payload, _tq, total_kv, _tn = st.pack_step(seqs)
+        ops.slot_table_update(st.table, msg, bs, n_payload)
+        indptr_buf = graph.get_input_buffer("paged_kv_indptr_buffer")
+        indices_buf = graph.get_input_buffer("paged_kv_indices_buffer")
+        last_buf = graph.get_input_buffer("paged_kv_last_page_len_buffer")
+        out_buf = graph.get_input_buffer("output_kv_indices_buffer")
+        # the reference never rewrites last_page_len on replay (stays 1 at page_size 1); for
+        # page_size > 1 it must be rebuilt
+        ops.build_meta(st.table, msg, bs, padded_bs, self.page_size, True, None, indptr_buf, indices_buf,
+                       None if self.page_size == 1 else last_buf, out_buf, self._graph_scratch)
+        plan = self._graph_plans[padded_bs]
+        return AttentionMetadata(forward_mode=batch.forward_mode, kv_cache=self.kv_cache,
+                                 output_kv_indices=out_buf[:padded_bs], wrapper=plan)
+
+
+# =======================================================================================================
+# module side
+# =======================================================================================================
+@contextmanager
+def attention_kv_cache(model: nn.Module, metadata: AttentionMetadata):
+    """Reference :297-306."""
+    mods = [m for m in model.modules() if isinstance(m, Attention)]
+    for m in mods:
+        m.set_attention_metadata(metadata)
+    yield
+    for m in mods:
+        m.set_attention_metadata(None)
+
+
+class Attention(nn.Module):
+    """Reference :310-373: store this step's K/V into the pool, then paged attention."""
+
+    def __init__(self, num_heads: int, head_dim: int, scaling: Optional[float], num_kv_heads: int, layer_id: int):
+        super().__init__()
+        self.num_heads = num_heads
+        self.head_dim = head_dim
+        self.num_kv_heads = num_kv_heads
+        self.num_kv_groups = num_heads // num_kv_heads
+        self.scaling = self.head_dim ** -0.5 if scaling is None else scaling
+        self.layer_id = layer_id
+        self.attention_metadata: Optional[AttentionMetadata] = None
+
+    def set_attention_metadata(self, metadata: Optional[AttentionMetadata]) -> None:
+        self.attention_metadata = metadata
+
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, save_kv_cache: bool = True):
+        md = self.attention_metadata
+        assert md is not None
+        q = q.contiguous()
+        if k is not None:
+            assert v is not None
+            if save_kv_cache:
+                md.kv_cache.set_kv_cache(self.layer_id, md.output_kv_indices,
+                                         k.view(-1, self.num_kv_heads, self.head_dim),
+                                         v.view(-1, self.num_kv_heads, self.head_dim))
+        q = q.view(-1, self.num_heads, self.head_dim)
+        k_cache, v_cache = md.kv_cache.get_kv_cache(self.layer_id)
+        name = mode_name(md.forward_mode)
+        if name not in ("PREFILL", "DECODE"):
+            raise NotImplementedError(name)
+        md.wrapper._sm_scale = self.scaling
+        o = md.wrapper.run(q, (k_cache, v_cache))
+        return o.view(-1, self.num_heads * self.head_dim)
