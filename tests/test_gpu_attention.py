@@ -1,0 +1,228 @@
+"""GPU: decode / prefill attention through the C ABI vs the fp32 oracle (tolerances in tests/util.py),
+the module-level API incl. CUDA-graph capture/replay, and size-independent properties."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import paged_attention_oracle as orc
+from tests.util import check_close, dev, make_paged_case
+
+pytestmark = pytest.mark.gpu
+
+
+def _ws(pkg, B, Hq, Hkv, D, total_q=1):
+    n = max(pkg.ops.decode_workspace_bytes(max(B, 1), Hq, Hkv, D), pkg.ops.prefill_workspace_bytes(max(B, 1), total_q, Hq, Hkv, D))
+    return torch.empty(n, dtype=torch.uint8, device="cuda")
+
+
+def run_decode(pkg, case):
+    d = dev(case)
+    ws = _ws(pkg, case["B"], case["Hq"], case["Hkv"], case["D"])
+    return pkg.ops.decode(d["q"], d["k_cache"], d["v_cache"], d["kv_indptr"], d["kv_indices"], d["last_page_len"],
+                          ws, case["page_size"], case["D"] ** -0.5)
+
+
+def run_prefill(pkg, case, causal=True):
+    d = dev(case)
+    ws = _ws(pkg, case["B"], case["Hq"], case["Hkv"], case["D"], int(case["qo_indptr"][-1]))
+    return pkg.ops.prefill(d["q"], d["k_cache"], d["v_cache"], d["qo_indptr"], d["kv_indptr"], d["kv_indices"],
+                           d["last_page_len"], ws, case["page_size"], case["D"] ** -0.5, causal)
+
+
+DECODE_CASES = [
+    # (kv_lens, Hq, Hkv, page_size)
+    ([1], 16, 8, 1), ([15, 16, 17, 1, 128, 129], 16, 8, 1), ([300, 5, 77, 1024], 32, 8, 1),
+    ([257, 33], 16, 4, 1), ([1000, 3, 64], 8, 2, 1), ([2000, 1, 31, 500], 4, 1, 1),
+    ([4097], 32, 8, 1), ([15, 16, 17, 40, 4000], 32, 8, 16), ([700, 9], 4, 1, 16), ([33, 600], 8, 2, 16),
+    ([50] * 300, 16, 8, 1), ([3000] * 40, 16, 8, 1), ([5, 0, 9], 16, 8, 1), ([20000, 10], 32, 8, 16),
+    ([129, 64], 8, 8, 1), ([90, 7], 64, 8, 1), ([45, 1100], 6, 3, 1), ([45, 1100], 32, 16, 1),
+]
+
+
+@pytest.mark.parametrize("kv_lens,Hq,Hkv,ps", DECODE_CASES)
+def test_decode_vs_oracle(pkg, kv_lens, Hq, Hkv, ps):
+    case = make_paged_case(kv_lens, Hq, Hkv, page_size=ps, seed=len(kv_lens) + Hq)
+    ref = orc.decode_attention(case["q"], case["k_cache"], case["v_cache"], case["kv_indptr"], case["kv_indices"],
+                               case["last_page_len"], ps, return_fp32=True)
+    out = run_decode(pkg, case)
+    check_close(out, ref, f"decode {kv_lens[:4]} Hq{Hq} Hkv{Hkv} ps{ps}")
+
+
+def test_decode_large_magnitude_and_repeat(pkg):
+    """Scores with a wide dynamic range (softmax stability) and run-to-run determinism."""
+    case = make_paged_case([900, 2500, 17], 32, 8, seed=11, scale=3.0)
+    ref = orc.decode_attention(case["q"], case["k_cache"], case["v_cache"], case["kv_indptr"], case["kv_indices"],
+                               case["last_page_len"], 1, return_fp32=True)
+    out1 = run_decode(pkg, case)
+    out2 = run_decode(pkg, case)
+    assert torch.equal(out1, out2)
+    out = out1.float().cpu()
+    assert (out - ref).abs().max() <= 2e-2 * max(1.0, ref.abs().max().item())
+    assert (out - ref).norm() / ref.norm() <= 1e-2
+
+
+PREFILL_CASES = [
+    # (q_lens, prefix_lens, Hq, Hkv, page_size)
+    ([5, 1, 130, 17], [0, 0, 0, 0], 16, 8, 1), ([64, 65, 63], [0, 0, 0], 8, 2, 1),
+    ([8, 1, 93, 64], [32, 32, 7, 0], 16, 8, 1), ([300], [0], 32, 8, 1), ([20, 40], [2048, 100], 8, 2, 1),
+    ([1, 1, 1], [9, 100, 0], 16, 8, 1), ([200, 31], [16, 48], 16, 8, 16), ([257], [0], 4, 1, 16),
+    ([700, 3], [0, 500], 32, 8, 1),
+]
+
+
+@pytest.mark.parametrize("q_lens,prefix,Hq,Hkv,ps", PREFILL_CASES)
+def test_prefill_vs_oracle(pkg, q_lens, prefix, Hq, Hkv, ps):
+    kv_lens = [a + b for a, b in zip(q_lens, prefix)]
+    case = make_paged_case(kv_lens, Hq, Hkv, page_size=ps, q_lens=q_lens, seed=sum(q_lens))
+    ref = orc.prefill_attention(case["q"], case["k_cache"], case["v_cache"], case["qo_indptr"], case["kv_indptr"],
+                                case["kv_indices"], case["last_page_len"], ps, return_fp32=True)
+    out = run_prefill(pkg, case)
+    check_close(out, ref, f"prefill q{q_lens} p{prefix} Hq{Hq} Hkv{Hkv} ps{ps}")
+
+
+def test_prefill_equals_decode_for_single_query(pkg):
+    case = make_paged_case([77, 1300, 16], 16, 8, seed=2)
+    a = run_decode(pkg, case).float()
+    b = run_prefill(pkg, case).float()
+    assert (a - b).abs().max() <= 1e-2
+
+
+# ---- module-level API: the call sequence of core/model_runner.py ----------------------------------
+class S:
+    def __init__(self, sid, token_ids, kv, cached):
+        self.seq_id, self.token_ids, self.kv_indices, self.cached_kv_len = sid, token_ids, kv, cached
+
+
+class Batch:
+    def __init__(self, mode, seqs):
+        self.forward_mode, self.seqs, self.num_seqs = mode, seqs, len(seqs)
+
+
+class TinyModel(torch.nn.Module):
+    def __init__(self, pkg, Hq, Hkv, D, layers):
+        super().__init__()
+        self.attn = torch.nn.ModuleList([pkg.Attention(Hq, D, None, Hkv, i) for i in range(layers)])
+
+
+def _oracle_step(pool_k, pool_v, layer, q, k, v, seqs, Hq, Hkv, D):
+    md = orc.build_metadata([orc.SeqView(len(s.token_ids), s.kv_indices, s.cached_kv_len) for s in seqs])
+    orc.store_kvcache(k.view(-1, Hkv, D), v.view(-1, Hkv, D), pool_k[layer], pool_v[layer], torch.from_numpy(md.output_kv_indices))
+    return orc.paged_attention(q.view(-1, Hq, D), pool_k[layer], pool_v[layer], md.qo_indptr, md.paged_kv_indptr,
+                               md.paged_kv_indices, md.paged_kv_last_page_len, 1, causal=True, return_fp32=True)
+
+
+@pytest.mark.parametrize("Hq,Hkv", [(16, 8), (8, 2), (4, 1)])
+def test_attention_module_prefill_decode_and_cuda_graph(pkg, Hq, Hkv):
+    D, L, num_slots, max_bs, ctx = 128, 2, 4096, 8, 256
+    devc = torch.device("cuda")
+    pool = pkg.KVCachePool(torch.bfloat16, devc, num_slots, L, Hkv, D)
+    pool.k_cache.zero_(); pool.v_cache.zero_()
+    ref_k = torch.zeros((L, num_slots, Hkv, D), dtype=torch.bfloat16)
+    ref_v = torch.zeros_like(ref_k)
+    be = pkg.AttentionBackend(pool, Hq, Hkv, D, torch.bfloat16, devc)
+    model = TinyModel(pkg, Hq, Hkv, D, L).to(devc)
+    g = torch.Generator().manual_seed(1)
+    rng = np.random.default_rng(1)
+    free = [int(x) for x in rng.permutation(num_slots)]
+    seqs = []
+    for i, n in enumerate([37, 5, 120]):
+        seqs.append(S(f"s{i}", [0] * n, [free.pop() for _ in range(n)], 0))
+
+    def rand(T, H):
+        return torch.randn((T, H * D), generator=g).to(torch.bfloat16)
+
+    def run_eager(batch, mode):
+        T = sum(len(s.token_ids) - s.cached_kv_len for s in batch)
+        md = be.build_metadata(Batch(mode, batch))
+        with pkg.attention_kv_cache(model, md):
+            for layer in range(L):
+                q, k, v = rand(T, Hq), rand(T, Hkv), rand(T, Hkv)
+                # v arrives as a strided view of a fused qkv buffer in the reference (qwen3.py:123)
+                qkv = torch.cat([q, k, v], dim=1).to(devc)
+                out = model.attn[layer](qkv[:, :Hq * D], qkv[:, Hq * D:(Hq + Hkv) * D].contiguous(), qkv[:, (Hq + Hkv) * D:])
+                ref = _oracle_step(ref_k, ref_v, layer, q, k, v, batch, Hq, Hkv, D)
+                check_close(out.view(-1, Hq, D), ref, f"{mode} layer {layer}")
+        assert all(m.attention_metadata is None for m in model.attn)
+
+    run_eager(seqs, pkg.ForwardMode.PREFILL)
+    for _ in range(3):
+        for s in seqs:
+            s.cached_kv_len = len(s.kv_indices); s.token_ids.append(0); s.kv_indices.append(free.pop())
+        run_eager(seqs, pkg.ForwardMode.DECODE)
+    assert torch.equal(pool.k_cache.cpu().view(torch.int16), ref_k.view(torch.int16))   # slot writes bit-exact
+
+    # ---- CUDA graph capture (model_runner.py:332-417) and replay (:276-316) ----
+    graph = pkg.CUDAGraph()
+    be.prepare_for_cuda_graph_capture(graph, max_bs, ctx)
+    static = {bs: dict(qkv=torch.zeros((bs, (Hq + 2 * Hkv) * D), dtype=torch.bfloat16, device=devc),
+                       out=torch.zeros((L, bs, Hq * D), dtype=torch.bfloat16, device=devc)) for bs in (8, 4, 2, 1)}
+
+    def fwd(bs):
+        qkv = static[bs]["qkv"]
+        for layer in range(L):
+            o = model.attn[layer](qkv[:, :Hq * D], qkv[:, Hq * D:(Hq + Hkv) * D].contiguous(), qkv[:, (Hq + Hkv) * D:])
+            static[bs]["out"][layer].copy_(o)
+
+    for bs in (8, 4, 2, 1):
+        md = be.build_metadata_for_cuda_graph_capture(graph, bs, ctx)
+        with pkg.attention_kv_cache(model, md):
+            fwd(bs)
+            with graph.capture(bs):
+                fwd(bs)
+        torch.cuda.synchronize()
+    pool.k_cache.copy_(ref_k); pool.v_cache.copy_(ref_v)   # capture warm-ups wrote slot 0; restore
+
+    for step in range(4):
+        batch = seqs if step != 2 else seqs[:1]
+        for s in batch:
+            s.cached_kv_len = len(s.kv_indices); s.token_ids.append(0); s.kv_indices.append(free.pop())
+        bs = len(batch)
+        padded = graph.match_bs(bs)
+        q, k, v = rand(bs, Hq), rand(bs, Hkv), rand(bs, Hkv)
+        static[padded]["qkv"].zero_()
+        static[padded]["qkv"][:bs].copy_(torch.cat([q, k, v], dim=1))
+        md = be.build_metadata_for_cuda_graph_replay(graph, Batch(pkg.ForwardMode.DECODE, batch), padded)
+        with pkg.attention_kv_cache(model, md):
+            graph.replay(padded)
+        for layer in range(L):
+            ref = _oracle_step(ref_k, ref_v, layer, q, k, v, batch, Hq, Hkv, D)
+            check_close(static[padded]["out"][layer][:bs].view(-1, Hq, D), ref, f"graph replay step {step} layer {layer}")
+    # padding rows must not have written anything: pools still identical, bit for bit
+    assert torch.equal(pool.k_cache.cpu().view(torch.int16), ref_k.view(torch.int16))
+    assert torch.equal(pool.v_cache.cpu().view(torch.int16), ref_v.view(torch.int16))
+
+
+# ---- size-independent properties at (near) full size ------------------------------------------------
+def test_decode_properties_long_context(pkg):
+    """B=8 x 32k tokens, page 16, Hq32/Hkv8 (config 5 shapes, 1/8 of the batch).
+    (1) V == const  =>  out == const exactly representable; (2) permuting a sequence's pages (and the
+    tokens with them) leaves the output unchanged up to fp32 summation order; (3) linear in V."""
+    torch.manual_seed(0)
+    B, L, ps, Hq, Hkv, D = 8, 32768, 16, 32, 8, 128
+    n_pages = B * L // ps
+    k_cache = torch.randn((n_pages * ps, Hkv, D), device="cuda", dtype=torch.bfloat16)
+    v1 = torch.randn_like(k_cache)
+    q = torch.randn((B, Hq, D), device="cuda", dtype=torch.bfloat16)
+    perm = torch.randperm(n_pages, device="cuda", dtype=torch.int32)
+    indptr = (torch.arange(B + 1, device="cuda", dtype=torch.int32) * (L // ps))
+    last = torch.full((B,), ps, device="cuda", dtype=torch.int32)
+    ws = _ws(pkg, B, Hq, Hkv, D)
+    sm = D ** -0.5
+    run = lambda v, idx: pkg.ops.decode(q, k_cache, v, indptr, idx, last, ws, ps, sm).float()
+    vc = torch.full_like(v1, 0.75)
+    assert (run(vc, perm) - 0.75).abs().max() <= 1e-2
+    o1 = run(v1, perm)
+    # reverse page order inside every sequence
+    rev = perm.view(B, -1).flip(1).contiguous().view(-1)
+    o2 = run(v1, rev)
+    assert (o1 - o2).abs().max() <= 1e-2
+    v2 = torch.randn_like(v1)
+    o12 = run((v1.float() + v2.float()).to(torch.bfloat16), perm)
+    assert (o12 - (o1 + run(v2, perm))).abs().max() <= 2e-2
+    # spot check one (sequence, head) against a direct fp32 computation on the device
+    b, h = 3, 17
+    pages = perm.view(B, -1)[b].long()
+    slots = (pages[:, None] * ps + torch.arange(ps, device="cuda")[None]).view(-1)
+    K = k_cache[slots, h // 4].float(); V = v1[slots, h // 4].float()
+    p = torch.softmax((K @ q[b, h].float()) * sm, 0)
+    assert (o1[b, h] - p @ V).abs().max() <= 2e-2
