@@ -43,13 +43,13 @@ NOMINAL_HBM_GBS = 8000.0   # north_star's "roughly 8 TB/s per B200"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--ctx", type=int, default=32768)
     ap.add_argument("--page-size", type=int, default=16)
-    ap.add_argument("--cpu-sample-seqs", type=int, default=2)
+    ap.add_argument("--cpu-sample-seqs", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -104,7 +104,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.02)
 
     def __enter__(self):
         if self.nv is not None:
@@ -133,8 +133,8 @@ def cpu_port_gbps(B_sample, L, Hq, Hkv, D, ps, steps=1, warmup=0):
     torch.set_num_threads(threads)
     g = torch.Generator().manual_seed(0)
     n_pages = B_sample * (L // ps)
-    k_cache = torch.randn((n_pages * ps, Hkv, D), generator=g).to(torch.bfloat16)
-    v_cache = torch.randn((n_pages * ps, Hkv, D), generator=g).to(torch.bfloat16)
+    k_cache = torch.randn((n_pages * ps, Hkv, D), generator=g, dtype=torch.bfloat16)
+    v_cache = torch.randn((n_pages * ps, Hkv, D), generator=g, dtype=torch.bfloat16)
     q = torch.randn((B_sample, Hq, D), generator=g).to(torch.bfloat16)
     k_new = torch.randn((B_sample, Hkv, D), generator=g).to(torch.bfloat16)
     v_new = torch.randn((B_sample, Hkv, D), generator=g).to(torch.bfloat16)
@@ -339,9 +339,10 @@ def run_b200_arm(args):
     # ---- (C) CPU baseline (rank 0, N=1 only) -----------------------------------------------------------
     cpu = None
     if rank == 0 and tp == 1 and not args.no_cpu_baseline:
-        val, dt, threads = cpu_port_gbps(args.cpu_sample_seqs, L, Hq, Hkv, D, ps, steps=1, warmup=0)
+        n_pass = 12
+        val, dt, threads = cpu_port_gbps(args.cpu_sample_seqs, L, Hq, Hkv, D, ps, steps=n_pass, warmup=1)
         cpu = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"{args.cpu_sample_seqs} of {B} sequences x {L} tokens (same shapes), 1 pass, {dt:.1f} s"}
+               "sample": f"{args.cpu_sample_seqs} of {B} sequences x {L} tokens (same shapes), {n_pass} passes of {dt:.2f} s"}
 
     traffic = None
     try:
