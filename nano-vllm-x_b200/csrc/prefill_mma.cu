@@ -7,7 +7,10 @@
 // double buffered; q.K^T and p.V on mma.sync m16n8k16 with fp32 online softmax; bottom-right
 // aligned causal mask (query j sees kv positions <= Lkv - Lq + j).  The tcgen05/TMEM kernel
 // (prefill_sm100.cu) supersedes it for the shapes it covers.
+#include <cstdlib>
+
 #include "common.cuh"
+#include "prefill_params.cuh"
 
 namespace b200 {
 
@@ -21,19 +24,6 @@ constexpr int kKVBytes = kKVTile * kPRowBytes;      // 16 KiB per K or V tile
 constexpr int kPStages = 2;
 constexpr int kPrefillSmem = kQBytes + kPStages * 2 * kKVBytes;  // 80 KiB
 
-struct PrefillParams {
-  const __nv_bfloat16* q;
-  const __nv_bfloat16* k_cache;
-  const __nv_bfloat16* v_cache;
-  const int32_t* qo_indptr;
-  const int32_t* kv_indptr;
-  const int32_t* kv_indices;
-  const int32_t* last_page_len;
-  __nv_bfloat16* out;
-  int64_t q_row_stride, out_row_stride, kv_slot_stride;
-  int B, Hq, Hkv, group, log2_ps, causal;
-  float scale_log2;
-};
 
 __global__ void __launch_bounds__(kPWarps * 32, 2) prefill_mma_kernel(const PrefillParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -299,5 +289,9 @@ extern "C" int b200_prefill(const void* q, int64_t q_row_stride, const void* k_c
   p.kv_slot_stride = kv_slot_stride;
   p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.group = Hq / Hkv; p.log2_ps = log2_ps; p.causal = causal ? 1 : 0;
   p.scale_log2 = sm_scale * kLog2e;
+  // tcgen05/TMEM kernel for every shape it covers; the mma.sync kernel only for GQA groups that do
+  // not pack into a 128-row tile.  B200ATTN_PREFILL=mma forces the latter (A/B measurements only).
+  static const bool force_mma = [] { const char* e = getenv("B200ATTN_PREFILL"); return e && e[0] == 'm'; }();
+  if (!force_mma && prefill_sm100_supports(p.group)) return launch_prefill_sm100(p, total_q, (cudaStream_t)stream);
   return launch_prefill_mma(p, total_q, (cudaStream_t)stream);
 }
