@@ -15,6 +15,8 @@
 // Double-buffered: tile t+1 streams in while tile t is on the tensor cores.
 // O lives in TMEM across the KV loop; a row is rescaled in place (tcgen05.ld/st) only when its
 // running max moves.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "prefill_params.cuh"
 #include "sm100.cuh"
@@ -43,7 +45,7 @@ __global__ void __launch_bounds__(128, 1) prefill_sm100_kernel(const PrefillPara
   __shared__ uint32_t s_tmem;
   __shared__ __align__(8) uint64_t s_bar[2];
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5;
   const int kvh = blockIdx.y;
   const int G = 1 << log2_g;
   const int tok_per_tile = kTM >> log2_g;
@@ -291,6 +293,340 @@ __global__ void __launch_bounds__(128, 1) prefill_sm100_kernel(const PrefillPara
   if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
+
+// =====================================================================================================
+// Stage 2: warp-specialised, two query tiles per CTA in ping-pong (the production path).
+//
+//   warps 0-3   softmax group 0  (rows   0..127 of the CTA's 256 packed rows; thread == row == TMEM lane)
+//   warps 4-7   softmax group 1  (rows 128..255)
+//   warp  8     MMA issuer (one thread): S_t = Q_t K^T, O_t += P_t V, t = 0,1
+//   warps 9-10  K/V/Q loaders: 16-byte cp.async gathers through the page table into a 4-slot ring
+//               of SWIZZLE_128B tiles (K0,V0,K1,V1,...), released by tcgen05.commit
+//
+// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512).  P_t (bf16) is written by
+// tcgen05.st over the first 64 columns of S_t and consumed as the TMEM A operand of the PV MMA, so P
+// never touches shared memory.  Issue order per KV tile j:  PV0(j) QK0(j+1) PV1(j) QK1(j+1): while
+// softmax group 0 works on S0(j+1) the tensor core runs PV1(j)/QK1(j+1) and vice versa.  The two
+// query tiles share every K/V tile, which halves L2->smem traffic per FLOP (a 128-row tile alone is
+// L2-bandwidth bound at ~40 B/clk/SM).
+// O rows are rescaled lazily: only when the row max grew by more than 2^8 since the scale in use
+// (exact: O and l carry the same stale scale until the final division).
+// =====================================================================================================
+constexpr int kWsThreads = 384;   // 3 warpgroups: softmax0, softmax1, {MMA, 2 loaders, 1 spare}
+constexpr int kWsLoaders = 64;
+constexpr int kRing = 4;
+constexpr int kWsOffQ = 0;                           // 2 x 32 KiB
+constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
+constexpr int kWsSmem = kWsOffRing + kRing * kTileBytes2 + 1024;
+constexpr float kLazyTau = 8.0f;
+
+__global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const PrefillParams p, const int log2_g) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ int s_scan[kWsThreads / 32 + 1];
+  __shared__ int s_loc[2];
+  __shared__ uint32_t s_tmem;
+  __shared__ __align__(8) uint64_t s_bar[1 + 2 * kRing + 6];
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kvh = blockIdx.y;
+  const int G = 1 << log2_g;
+  const int tok_per_tile = kTM >> log2_g;        // tokens per 128-row tile
+  const int tok_per_cta = 2 * tok_per_tile;
+
+  {
+    const int target = blockIdx.x;
+    int carry = 0;
+    bool found = false;
+    for (int base = 0; base < p.B; base += kWsThreads) {
+      const int i = base + tid;
+      int t = 0;
+      if (i < p.B) t = (p.qo_indptr[i + 1] - p.qo_indptr[i] + tok_per_cta - 1) / tok_per_cta;
+      int blk;
+      const int incl = block_inclusive_scan<kWsThreads>(t, s_scan, &blk) + carry;
+      const int excl = incl - t;
+      if (t > 0 && excl <= target && target < incl) {
+        s_loc[0] = i;
+        s_loc[1] = target - excl;
+      }
+      carry += blk;
+      if (carry > target) {
+        found = true;
+        break;
+      }
+    }
+    __syncthreads();
+    if (!found) return;
+  }
+  const int s = s_loc[0];
+  const int q0 = p.qo_indptr[s];
+  const int Lq = p.qo_indptr[s + 1] - q0;
+  const int j0 = s_loc[1] * tok_per_cta;
+  const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
+  const int toks0 = max(0, min(tok_per_tile, Lq - j0)), toks1 = max(0, min(tok_per_tile, Lq - j0 - tok_per_tile));
+  int kvhi0 = p.causal ? min(Lkv, Lkv - Lq + j0 + toks0) : Lkv;
+  int kvhi1 = p.causal ? min(Lkv, Lkv - Lq + j0 + tok_per_tile + toks1) : Lkv;
+  if (kvhi0 < 0 || toks0 == 0) kvhi0 = 0;
+  if (kvhi1 < 0 || toks1 == 0) kvhi1 = 0;
+  const int nt0 = (kvhi0 + kTN - 1) / kTN, nt1 = (kvhi1 + kTN - 1) / kTN;
+  const int J = max(nt0, nt1);
+  const int kv_hi_all = max(kvhi0, kvhi1);
+
+  const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar0 = smem_u32(&s_bar[0]);
+  const uint32_t bar_q = bar0;
+  auto bar_full = [&](int slot) { return bar0 + 8u * (1 + slot); };
+  auto bar_empty = [&](int slot) { return bar0 + 8u * (1 + kRing + slot); };
+  auto bar_s = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + t); };
+  auto bar_p = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + 2 + t); };
+  auto bar_o = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + 4 + t); };
+
+  if (tid == 0) {
+    mbar_init(bar_q, kWsLoaders);
+    for (int i = 0; i < kRing; ++i) {
+      mbar_init(bar_full(i), kWsLoaders);
+      mbar_init(bar_empty(i), 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(bar_s(t), 1);
+      mbar_init(bar_p(t), 128);
+      mbar_init(bar_o(t), 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&s_tmem), 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  if (warp >= 11) {
+    // spare warp of the third warpgroup: only takes part in the register hand-over
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+  } else if (warp >= 9) {
+    // =================================== loaders ==========================================================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+    const int lt = tid - 9 * 32;                    // 0..63
+    const int gc = lt & 15, lrow0 = lt >> 4;        // rows lrow0 + 4*i
+    const uint32_t chunk_off = (uint32_t)(gc >> 3) * kBlkBytes;
+    const int c8 = gc & 7;
+    const int page0 = p.kv_indptr[s];
+    const int ps_mask = (1 << p.log2_ps) - 1;
+    const int rows_total = (toks0 + toks1) << log2_g;
+#pragma unroll 4
+    for (int i = 0; i < 256 / 4; ++i) {
+      const int R = lrow0 + 4 * i;                  // packed row 0..255
+      const bool ok = R < rows_total;
+      const int tok = j0 + (R >> log2_g), head = kvh * G + (R & (G - 1));
+      const __nv_bfloat16* src = p.q + (int64_t)(q0 + (ok ? tok : j0)) * p.q_row_stride + (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
+      const int r = R & 127;
+      cp_async_16(smem + kWsOffQ + (R >> 7) * kTileBytes2 + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src, ok ? 16u : 0u);
+    }
+    cp_async_commit();
+    const int N = 2 * J;
+    for (int n = 0; n < N; ++n) {
+      const int slot = n % kRing, use = n / kRing;
+      mbar_wait(bar_empty(slot), (use & 1) ^ 1);
+      const int tile = n >> 1;
+      const __nv_bfloat16* base = (n & 1) ? p.v_cache : p.k_cache;
+      const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2 + chunk_off;
+#pragma unroll 8
+      for (int i = 0; i < kTN / 4; ++i) {
+        const int r = lrow0 + 4 * i;
+        const int tok = tile * kTN + r;
+        const bool ok = tok < kv_hi_all;
+        int64_t off = (int64_t)kvh * kTD + gc * 8;
+        if (ok) {
+          const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
+          off += ((int64_t)(page << p.log2_ps) + (tok & ps_mask)) * p.kv_slot_stride;
+        }
+        cp_async_16(dst0 + r * 128 + ((c8 ^ (r & 7)) << 4), base + off, ok ? 16u : 0u);
+      }
+      cp_async_commit();
+      cp_async_wait<1>();              // everything but the fill just issued has landed
+      fence_proxy_async_smem();
+      if (n == 0) mbar_arrive(bar_q); else mbar_arrive(bar_full((n - 1) % kRing));
+    }
+    cp_async_wait<0>();
+    fence_proxy_async_smem();
+    if (N == 0) mbar_arrive(bar_q); else mbar_arrive(bar_full((N - 1) % kRing));
+  } else if (warp == 8) {
+    // =================================== MMA issuer =======================================================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+    if ((tid & 31) == 0 && J > 0) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
+      auto ring = [&](int n) { return smem + kWsOffRing + (n % kRing) * kTileBytes2; };
+      auto issue_qk = [&](int t, int j) {
+        const uint32_t kst = ring(2 * j), qst = smem + kWsOffQ + t * kTileBytes2;
+#pragma unroll
+        for (int ks = 0; ks < kTD / 16; ++ks) {
+          const uint32_t koff = (uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32;
+          umma_ss(tmem + t * kTN, make_smem_desc(qst + koff, 16, 1024), make_smem_desc(kst + koff, 16, 1024), idesc_qk, ks > 0);
+        }
+        umma_commit(bar_s(t));
+      };
+      auto issue_pv = [&](int t, int j) {
+        const uint32_t vst = ring(2 * j + 1);
+#pragma unroll
+        for (int ks = 0; ks < kTN / 16; ++ks)
+          umma_ts(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, make_smem_desc(vst + ks * 2048, kBlkBytes, 1024), idesc_pv,
+                  (j > 0 || ks > 0));
+      };
+      mbar_wait(bar_q, 0);
+      mbar_wait(bar_full(0), 0);
+      tc_fence_after();
+      if (nt0 > 0) issue_qk(0, 0);
+      if (nt1 > 0) issue_qk(1, 0);
+      umma_commit(bar_empty(0));                                       // K(0) free once both QK(0) are done
+      for (int j = 0; j < J; ++j) {
+        const int nv = 2 * j + 1, nk = 2 * j + 2;
+        mbar_wait(bar_full(nv % kRing), (nv / kRing) & 1);             // V(j)
+        bool k_ready = false;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          const int ntt = t ? nt1 : nt0;
+          if (j < ntt) {
+            mbar_wait(bar_p(t), j & 1);                                // P_t(j) is in TMEM
+            tc_fence_after();
+            issue_pv(t, j);
+            if (j == ntt - 1) umma_commit(bar_o(t));
+          }
+          if (j + 1 < ntt) {
+            if (!k_ready) {
+              mbar_wait(bar_full(nk % kRing), (nk / kRing) & 1);       // K(j+1)
+              tc_fence_after();
+              k_ready = true;
+            }
+            issue_qk(t, j + 1);
+          }
+        }
+        umma_commit(bar_empty(nv % kRing));
+        if (j + 1 < J) umma_commit(bar_empty(nk % kRing));
+      }
+    }
+  } else {
+    // =================================== softmax groups ===================================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 200;\n");
+    const int t = warp >> 2;                          // query tile 0/1
+    const int r = tid & 127;                          // row in the tile == TMEM lane
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem + lane_base + t * kTN;
+    const uint32_t tO = tmem + lane_base + 2 * kTN + t * kTD;
+    const int my_tok = j0 + t * tok_per_tile + (r >> log2_g);
+    const int lim = p.causal ? (Lkv - Lq + my_tok) : (Lkv - 1);
+    const int lim0 = p.causal ? (Lkv - Lq + j0 + t * tok_per_tile) : (Lkv - 1);
+    const int kv_hi = t ? kvhi1 : kvhi0;
+    const int ntt = t ? nt1 : nt0;
+    const int tokst = t ? toks1 : toks0;
+    float m_used = 0.f, l_run = 0.f;
+    for (int j = 0; j < ntt; ++j) {
+      mbar_wait(bar_s(t), j & 1);
+      tc_fence_after();
+      uint32_t sv[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+      tmem_wait_ld();
+      const int kv0 = j * kTN;
+      const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
+      float mx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          float x = __uint_as_float(sv[c][e]);
+          if (need_mask) {
+            const int kvp = kv0 + c * 32 + e;
+            if (kvp > lim || kvp >= kv_hi) x = -INFINITY;
+            sv[c][e] = __float_as_uint(x);
+          }
+          mx = fmaxf(mx, x);
+        }
+      }
+      mx *= p.scale_log2;                             // scale > 0: max commutes with it
+      // lazy rescale decision
+      float alpha = 1.f;
+      bool grow;
+      if (l_run == 0.f) {                             // nothing accumulated yet: adopt this tile's max
+        grow = false;
+        if (mx != -INFINITY) m_used = mx;
+      } else {
+        grow = mx > m_used + kLazyTau;
+        if (grow) {
+          alpha = fast_exp2(m_used - mx);
+          m_used = mx;
+        }
+      }
+      if (j > 0 && __any_sync(0xffffffffu, grow)) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t ov[32];
+          tmem_ld_32x32b_x32(tO + c * 32, ov);
+          tmem_wait_ld();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
+          tmem_st_32x32b_x32(tO + c * 32, ov);
+        }
+      }
+      l_run *= alpha;
+      const float neg_m = -m_used;
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pw[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float a = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e]), p.scale_log2, neg_m));
+          const float b = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e + 1]), p.scale_log2, neg_m));
+          sum += a + b;
+          pw[e] = pack_bf16x2(a, b);
+        }
+        tmem_st_32x32b_x16(tS + c * 16, pw);          // P_t: 64 packed columns over S_t
+      }
+      l_run += sum;
+      tmem_wait_st();
+      tc_fence_before();
+      mbar_arrive(bar_p(t));
+    }
+    // ---- epilogue -------------------------------------------------------------------------------------------
+    const bool has = ntt > 0;
+    if (has) {
+      mbar_wait(bar_o(t), 0);
+      tc_fence_after();
+    }
+    const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+    const bool row_ok = r < (tokst << log2_g);
+    __nv_bfloat16* dst = p.out + (int64_t)(q0 + (row_ok ? my_tok : j0)) * p.out_row_stride + (int64_t)(kvh * G + (r & (G - 1))) * kTD;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t ov[32];
+      if (has) {
+        tmem_ld_32x32b_x32(tO + c * 32, ov);
+        tmem_wait_ld();
+      } else {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) ov[e] = 0u;
+      }
+      if (row_ok) {
+#pragma unroll
+        for (int j8 = 0; j8 < 4; ++j8) {
+          uint4 w;
+          w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+          w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+          w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+          w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(dst + c * 32 + j8 * 8) = w;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
 int launch_prefill_sm100(const PrefillParams& p, int total_q, cudaStream_t st) {
   int log2_g = 0;
   while ((1 << log2_g) < p.group) ++log2_g;
@@ -300,10 +636,22 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, cudaStream_t st) {
     if (e != cudaSuccess) return fail("b200_prefill(sm100): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     attr_set = true;
   }
+  static const bool stage1 = [] { const char* e = getenv("B200ATTN_PREFILL"); return e && e[0] == 's'; }();
   const int tok_per_tile = kTM >> log2_g;
-  const int max_q_tiles = total_q / tok_per_tile + p.B;   // >= sum_i ceil(Lq_i / tok_per_tile)
-  prefill_sm100_kernel<<<dim3(max_q_tiles, p.Hkv), 128, kSm100Smem, st>>>(p, log2_g);
-  return check_launch("b200_prefill(sm100)");
+  if (stage1) {   // single-tile serial kernel, kept for A/B measurements (B200ATTN_PREFILL=s1)
+    const int max_q_tiles = total_q / tok_per_tile + p.B;   // >= sum_i ceil(Lq_i / tok_per_tile)
+    prefill_sm100_kernel<<<dim3(max_q_tiles, p.Hkv), 128, kSm100Smem, st>>>(p, log2_g);
+    return check_launch("b200_prefill(sm100 s1)");
+  }
+  static bool attr_ws = false;
+  if (!attr_ws) {
+    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
+    if (e != cudaSuccess) return fail("b200_prefill(sm100 ws): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_ws = true;
+  }
+  const int max_ctas = total_q / (2 * tok_per_tile) + p.B;
+  prefill_sm100_ws_kernel<<<dim3(max_ctas, p.Hkv), kWsThreads, kWsSmem, st>>>(p, log2_g);
+  return check_launch("b200_prefill(sm100 ws)");
 }
 
 bool prefill_sm100_supports(int group) { return group >= 1 && group <= 64 && (group & (group - 1)) == 0; }
