@@ -320,6 +320,74 @@ constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
 constexpr int kWsSmem = kWsOffRing + kRing * kTileBytes2 + 1024;
 constexpr float kLazyTau = 8.0f;
 
+// One softmax step of one row (thread) over a 128-column S tile held in TMEM.
+// MASK is a template parameter so the (rare) masked tiles do not tax the common path with
+// predicated-off instructions (nvcc if-converts a runtime `if` around the element loop).
+template <bool MASK>
+__device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
+                                             const float scale_log2, float& m_used, float& l_run) {
+  uint32_t sv[4][32];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+  tmem_wait_ld();
+  if (MASK) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+#pragma unroll
+      for (int e = 0; e < 32; ++e)
+        if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
+  }
+  float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int e = 0; e < 32; e += 4) {
+      mx0 = fmaxf(mx0, __uint_as_float(sv[c][e]));
+      mx1 = fmaxf(mx1, __uint_as_float(sv[c][e + 1]));
+      mx2 = fmaxf(mx2, __uint_as_float(sv[c][e + 2]));
+      mx3 = fmaxf(mx3, __uint_as_float(sv[c][e + 3]));
+    }
+  }
+  const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2;   // scale > 0: max commutes
+  float alpha = 1.f;
+  bool grow = false;
+  if (l_run == 0.f) {                      // nothing accumulated yet: adopt this tile's max
+    if (mx != -INFINITY) m_used = mx;
+  } else if (mx > m_used + kLazyTau) {
+    grow = true;
+    alpha = fast_exp2(m_used - mx);
+    m_used = mx;
+  }
+  if (first_pv_done && __any_sync(0xffffffffu, grow)) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t ov[32];
+      tmem_ld_32x32b_x32(tO + c * 32, ov);
+      tmem_wait_ld();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
+      tmem_st_32x32b_x32(tO + c * 32, ov);
+    }
+  }
+  const float neg_m = -m_used;
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint32_t pw[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const float a = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e]), scale_log2, neg_m));
+      const float b = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e + 1]), scale_log2, neg_m));
+      s0 += a;
+      s1 += b;
+      pw[e] = pack_bf16x2(a, b);
+    }
+    tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
+  }
+  l_run = l_run * alpha + (s0 + s1);
+  tmem_wait_st();
+}
+
 __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const PrefillParams p, const int log2_g) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_scan[kWsThreads / 32 + 1];
@@ -426,23 +494,41 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
     }
     cp_async_commit();
     const int N = 2 * J;
+    // Page-table lookups are taken off the critical path: lane l of loader warp w fetches the slots of
+    // rows 4l+2w and 4l+2w+1 of a tile ONE TILE AHEAD (coalesced), and the fills get them by shuffle.
+    const int lane = tid & 31, lw = warp - 9;
+    auto fetch_slots = [&](int tile, int& sa, int& sb) {
+      const int tok = tile * kTN + 4 * lane + 2 * lw;
+      sa = sb = -1;
+      if (tok < kv_hi_all) {
+        const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
+        sa = (page << p.log2_ps) + (tok & ps_mask);
+      }
+      if (tok + 1 < kv_hi_all) {
+        const int page = __ldg(p.kv_indices + page0 + ((tok + 1) >> p.log2_ps));
+        sb = (page << p.log2_ps) + ((tok + 1) & ps_mask);
+      }
+    };
+    int cur_a = -1, cur_b = -1, nxt_a = -1, nxt_b = -1;
+    if (J > 0) fetch_slots(0, nxt_a, nxt_b);
+    const bool hi_row = (lane >> 4) != 0;
     for (int n = 0; n < N; ++n) {
       const int slot = n % kRing, use = n / kRing;
-      mbar_wait(bar_empty(slot), (use & 1) ^ 1);
       const int tile = n >> 1;
-      const __nv_bfloat16* base = (n & 1) ? p.v_cache : p.k_cache;
+      if ((n & 1) == 0) {
+        cur_a = nxt_a; cur_b = nxt_b;
+        if (tile + 1 < J) fetch_slots(tile + 1, nxt_a, nxt_b);
+      }
+      mbar_wait(bar_empty(slot), (use & 1) ^ 1);
+      const __nv_bfloat16* base = ((n & 1) ? p.v_cache : p.k_cache) + (int64_t)kvh * kTD + gc * 8;
       const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2 + chunk_off;
 #pragma unroll 8
       for (int i = 0; i < kTN / 4; ++i) {
         const int r = lrow0 + 4 * i;
-        const int tok = tile * kTN + r;
-        const bool ok = tok < kv_hi_all;
-        int64_t off = (int64_t)kvh * kTD + gc * 8;
-        if (ok) {
-          const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
-          off += ((int64_t)(page << p.log2_ps) + (tok & ps_mask)) * p.kv_slot_stride;
-        }
-        cp_async_16(dst0 + r * 128 + ((c8 ^ (r & 7)) << 4), base + off, ok ? 16u : 0u);
+        const int sa = __shfl_sync(0xffffffffu, cur_a, i), sb = __shfl_sync(0xffffffffu, cur_b, i);
+        const int sl = hi_row ? sb : sa;
+        const bool ok = sl >= 0;
+        cp_async_16(dst0 + r * 128 + ((c8 ^ (r & 7)) << 4), base + (ok ? (int64_t)sl * p.kv_slot_stride : 0), ok ? 16u : 0u);
       }
       cp_async_commit();
       cp_async_wait<1>();              // everything but the fill just issued has landed
@@ -525,68 +611,14 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
     for (int j = 0; j < ntt; ++j) {
       mbar_wait(bar_s(t), j & 1);
       tc_fence_after();
-      uint32_t sv[4][32];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
-      tmem_wait_ld();
       const int kv0 = j * kTN;
       const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
-      float mx = -INFINITY;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-#pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          float x = __uint_as_float(sv[c][e]);
-          if (need_mask) {
-            const int kvp = kv0 + c * 32 + e;
-            if (kvp > lim || kvp >= kv_hi) x = -INFINITY;
-            sv[c][e] = __float_as_uint(x);
-          }
-          mx = fmaxf(mx, x);
-        }
-      }
-      mx *= p.scale_log2;                             // scale > 0: max commutes with it
-      // lazy rescale decision
-      float alpha = 1.f;
-      bool grow;
-      if (l_run == 0.f) {                             // nothing accumulated yet: adopt this tile's max
-        grow = false;
-        if (mx != -INFINITY) m_used = mx;
+      if (need_mask) {
+        const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
+        softmax_tile<true>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run);
       } else {
-        grow = mx > m_used + kLazyTau;
-        if (grow) {
-          alpha = fast_exp2(m_used - mx);
-          m_used = mx;
-        }
+        softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run);
       }
-      if (j > 0 && __any_sync(0xffffffffu, grow)) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t ov[32];
-          tmem_ld_32x32b_x32(tO + c * 32, ov);
-          tmem_wait_ld();
-#pragma unroll
-          for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
-          tmem_st_32x32b_x32(tO + c * 32, ov);
-        }
-      }
-      l_run *= alpha;
-      const float neg_m = -m_used;
-      float sum = 0.f;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t pw[16];
-#pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const float a = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e]), p.scale_log2, neg_m));
-          const float b = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e + 1]), p.scale_log2, neg_m));
-          sum += a + b;
-          pw[e] = pack_bf16x2(a, b);
-        }
-        tmem_st_32x32b_x16(tS + c * 16, pw);          // P_t: 64 packed columns over S_t
-      }
-      l_run += sum;
-      tmem_wait_st();
       tc_fence_before();
       mbar_arrive(bar_p(t));
     }
