@@ -325,7 +325,8 @@ constexpr float kLazyTau = 8.0f;
 // predicated-off instructions (nvcc if-converts a runtime `if` around the element loop).
 template <bool MASK>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
-                                             const float scale_log2, float& m_used, float& l_run) {
+                                             const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
+                                             const uint32_t bar_p1) {
   uint32_t sv[4][32];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
@@ -383,9 +384,13 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       pw[e] = pack_bf16x2(a, b);
     }
     tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
+    if (c == 1 || c == 3) {                         // hand P over in two halves: PV starts on the first
+      tmem_wait_st();                               // while the second is still in the exp unit
+      tc_fence_before();
+      mbar_arrive(c == 1 ? bar_p0 : bar_p1);
+    }
   }
   l_run = l_run * alpha + (s0 + s1);
-  tmem_wait_st();
 }
 
 __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const PrefillParams p, const int log2_g) {
@@ -393,7 +398,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
   __shared__ int s_scan[kWsThreads / 32 + 1];
   __shared__ int s_loc[2];
   __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[1 + 2 * kRing + 6];
+  __shared__ __align__(8) uint64_t s_bar[1 + 2 * kRing + 8];
+  __shared__ __align__(16) int s_slots[2][2][2][32];   // [tile parity][loader warp][row parity][i]
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int kvh = blockIdx.y;
@@ -445,8 +451,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
   auto bar_full = [&](int slot) { return bar0 + 8u * (1 + slot); };
   auto bar_empty = [&](int slot) { return bar0 + 8u * (1 + kRing + slot); };
   auto bar_s = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + t); };
-  auto bar_p = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + 2 + t); };
-  auto bar_o = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + 4 + t); };
+  auto bar_p = [&](int t, int half) { return bar0 + 8u * (1 + 2 * kRing + 2 + 2 * t + half); };
+  auto bar_o = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + 6 + t); };
 
   if (tid == 0) {
     mbar_init(bar_q, kWsLoaders);
@@ -456,7 +462,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
     }
     for (int t = 0; t < 2; ++t) {
       mbar_init(bar_s(t), 1);
-      mbar_init(bar_p(t), 128);
+      mbar_init(bar_p(t, 0), 128);
+      mbar_init(bar_p(t, 1), 128);
       mbar_init(bar_o(t), 1);
     }
     fence_mbar_init();
@@ -494,12 +501,15 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
     }
     cp_async_commit();
     const int N = 2 * J;
-    // Page-table lookups are taken off the critical path: lane l of loader warp w fetches the slots of
-    // rows 4l+2w and 4l+2w+1 of a tile ONE TILE AHEAD (coalesced), and the fills get them by shuffle.
+    // Page-table lookups are taken off the critical path: ONE TILE AHEAD, lane l of loader warp w fetches
+    // the slots of rows 4l+2w and 4l+2w+1 (coalesced) and parks them in shared memory; a fill then picks up
+    // its 32 row slots with 8 broadcast LDS.128.  The fill loop itself is ~7 instructions per 16-byte
+    // cp.async (the first version spent ~70 and made the loaders the bottleneck of the whole kernel).
     const int lane = tid & 31, lw = warp - 9;
-    auto fetch_slots = [&](int tile, int& sa, int& sb) {
+    const int hrow = lane >> 4;
+    auto fetch_slots = [&](int tile) {
       const int tok = tile * kTN + 4 * lane + 2 * lw;
-      sa = sb = -1;
+      int sa = -1, sb = -1;
       if (tok < kv_hi_all) {
         const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
         sa = (page << p.log2_ps) + (tok & ps_mask);
@@ -508,27 +518,44 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
         const int page = __ldg(p.kv_indices + page0 + ((tok + 1) >> p.log2_ps));
         sb = (page << p.log2_ps) + ((tok + 1) & ps_mask);
       }
+      s_slots[tile & 1][lw][0][lane] = sa;
+      s_slots[tile & 1][lw][1][lane] = sb;
     };
-    int cur_a = -1, cur_b = -1, nxt_a = -1, nxt_b = -1;
-    if (J > 0) fetch_slots(0, nxt_a, nxt_b);
-    const bool hi_row = (lane >> 4) != 0;
+    if (J > 0) fetch_slots(0);
+    const uint32_t stride_b = (uint32_t)(p.kv_slot_stride * 2);   // bytes between token slots (< 4 GiB)
+    const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)kvh * kTD + gc * 8);
+    const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)kvh * kTD + gc * 8);
+    // row r = lrow0 + 4i: byte offset r*128 = lrow0*128 + i*512; swizzle term depends on i's parity only
+    const uint32_t dst_even = chunk_off + lrow0 * 128 + ((c8 ^ lrow0) << 4);
+    const uint32_t dst_odd = chunk_off + lrow0 * 128 + ((c8 ^ (lrow0 + 4)) << 4);
+    int sl[32];
     for (int n = 0; n < N; ++n) {
       const int slot = n % kRing, use = n / kRing;
       const int tile = n >> 1;
       if ((n & 1) == 0) {
-        cur_a = nxt_a; cur_b = nxt_b;
-        if (tile + 1 < J) fetch_slots(tile + 1, nxt_a, nxt_b);
+        __syncwarp();
+        const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int4 v = src[i];
+          sl[4 * i] = v.x; sl[4 * i + 1] = v.y; sl[4 * i + 2] = v.z; sl[4 * i + 3] = v.w;
+        }
+        __syncwarp();
+        if (tile + 1 < J) fetch_slots(tile + 1);
       }
       mbar_wait(bar_empty(slot), (use & 1) ^ 1);
-      const __nv_bfloat16* base = ((n & 1) ? p.v_cache : p.k_cache) + (int64_t)kvh * kTD + gc * 8;
-      const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2 + chunk_off;
-#pragma unroll 8
-      for (int i = 0; i < kTN / 4; ++i) {
-        const int r = lrow0 + 4 * i;
-        const int sa = __shfl_sync(0xffffffffu, cur_a, i), sb = __shfl_sync(0xffffffffu, cur_b, i);
-        const int sl = hi_row ? sb : sa;
-        const bool ok = sl >= 0;
-        cp_async_16(dst0 + r * 128 + ((c8 ^ (r & 7)) << 4), base + (ok ? (int64_t)sl * p.kv_slot_stride : 0), ok ? 16u : 0u);
+      const char* base = (n & 1) ? vbase : kbase;
+      const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2;
+      if ((tile + 1) * kTN <= kv_hi_all) {            // full tile: no zero-fill predicates
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)sl[i] * stride_b, 16u);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const bool ok = sl[i] >= 0;
+          cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)(ok ? sl[i] : 0) * stride_b, ok ? 16u : 0u);
+        }
       }
       cp_async_commit();
       cp_async_wait<1>();              // everything but the fill just issued has landed
@@ -541,32 +568,35 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
   } else if (warp == 8) {
     // =================================== MMA issuer =======================================================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    if ((tid & 31) == 0 && J > 0) {
+    if (J > 0) {   // all 32 lanes run this (warp-uniform); one elected lane issues each tcgen05 op
       constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
-      auto ring = [&](int n) { return smem + kWsOffRing + (n % kRing) * kTileBytes2; };
+      const uint64_t qdesc0 = make_smem_desc(smem + kWsOffQ, 16, 1024);
+      const uint64_t kdesc0 = make_smem_desc(smem + kWsOffRing, 16, 1024);          // K tiles: K-major
+      const uint64_t vdesc0 = make_smem_desc(smem + kWsOffRing, kBlkBytes, 1024);   // V tiles: MN-major
       auto issue_qk = [&](int t, int j) {
-        const uint32_t kst = ring(2 * j), qst = smem + kWsOffQ + t * kTileBytes2;
+        const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
+        const uint64_t kd = kdesc0 + (uint64_t)(((2 * j) % kRing) * (kTileBytes2 >> 4));
 #pragma unroll
         for (int ks = 0; ks < kTD / 16; ++ks) {
-          const uint32_t koff = (uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32;
-          umma_ss(tmem + t * kTN, make_smem_desc(qst + koff, 16, 1024), make_smem_desc(kst + koff, 16, 1024), idesc_qk, ks > 0);
+          const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
+          umma_ss_elect(tmem + t * kTN, qd + koff, kd + koff, idesc_qk, ks > 0);
         }
-        umma_commit(bar_s(t));
+        umma_commit_elect(bar_s(t));
       };
-      auto issue_pv = [&](int t, int j) {
-        const uint32_t vst = ring(2 * j + 1);
+      auto issue_pv = [&](int t, int j, int half) {   // half of the 128 tokens of P/V (4 k-steps)
+        const uint64_t vd = vdesc0 + (uint64_t)(((2 * j + 1) % kRing) * (kTileBytes2 >> 4));
 #pragma unroll
-        for (int ks = 0; ks < kTN / 16; ++ks)
-          umma_ts(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, make_smem_desc(vst + ks * 2048, kBlkBytes, 1024), idesc_pv,
-                  (j > 0 || ks > 0));
+        for (int ks = half * 4; ks < half * 4 + 4; ++ks)
+          umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
+                        (j > 0 || ks > 0));
       };
       mbar_wait(bar_q, 0);
       mbar_wait(bar_full(0), 0);
       tc_fence_after();
       if (nt0 > 0) issue_qk(0, 0);
       if (nt1 > 0) issue_qk(1, 0);
-      umma_commit(bar_empty(0));                                       // K(0) free once both QK(0) are done
+      umma_commit_elect(bar_empty(0));                                 // K(0) free once both QK(0) are done
       for (int j = 0; j < J; ++j) {
         const int nv = 2 * j + 1, nk = 2 * j + 2;
         mbar_wait(bar_full(nv % kRing), (nv / kRing) & 1);             // V(j)
@@ -575,10 +605,13 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
         for (int t = 0; t < 2; ++t) {
           const int ntt = t ? nt1 : nt0;
           if (j < ntt) {
-            mbar_wait(bar_p(t), j & 1);                                // P_t(j) is in TMEM
+            mbar_wait(bar_p(t, 0), j & 1);                             // first 64 columns of P_t(j) are in TMEM
             tc_fence_after();
-            issue_pv(t, j);
-            if (j == ntt - 1) umma_commit(bar_o(t));
+            issue_pv(t, j, 0);
+            mbar_wait(bar_p(t, 1), j & 1);                             // the rest
+            tc_fence_after();
+            issue_pv(t, j, 1);
+            if (j == ntt - 1) umma_commit_elect(bar_o(t));
           }
           if (j + 1 < ntt) {
             if (!k_ready) {
@@ -589,8 +622,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
             issue_qk(t, j + 1);
           }
         }
-        umma_commit(bar_empty(nv % kRing));
-        if (j + 1 < J) umma_commit(bar_empty(nk % kRing));
+        umma_commit_elect(bar_empty(nv % kRing));
+        if (j + 1 < J) umma_commit_elect(bar_empty(nk % kRing));
       }
     }
   } else {
@@ -615,12 +648,10 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
       const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
       if (need_mask) {
         const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
-        softmax_tile<true>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run);
+        softmax_tile<true>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
       } else {
-        softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run);
+        softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
       }
-      tc_fence_before();
-      mbar_arrive(bar_p(t));
     }
     // ---- epilogue -------------------------------------------------------------------------------------------
     const bool has = ntt > 0;
