@@ -408,7 +408,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
   const int tok_per_cta = 2 * tok_per_tile;
 
   {
-    const int target = blockIdx.x;
+    const int target = gridDim.x - 1 - blockIdx.x;   // heaviest (latest) query tiles of a sequence launch first
     int carry = 0;
     bool found = false;
     for (int base = 0; base < p.B; base += kWsThreads) {
