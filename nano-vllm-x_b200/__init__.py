@@ -18,6 +18,25 @@ from .core.kv_cache import KVCachePool, store_kvcache              # noqa: F401
 from .layers.attention import (Attention, AttentionBackend, AttentionMetadata, AttentionPlan,  # noqa: F401
                                SlotTable, attention_kv_cache)
 
-__all__ = ["Attention", "AttentionBackend", "AttentionMetadata", "AttentionPlan", "SlotTable",
+
+
+def shard_heads(num_qo_heads: int, num_kv_heads: int, tp_size: int, tp_rank: int):
+    """Head ranges owned by one tensor-parallel rank, the partitioning the kernels inherit
+    (reference: core/model_runner.py:43-44, models/qwen3.py:73-86; KV heads are replicated when
+    tp_size > num_kv_heads, layers/linear.py:333-338).  No collective is needed on the attention path."""
+    assert num_qo_heads % tp_size == 0
+    hq = num_qo_heads // tp_size
+    q_heads = range(tp_rank * hq, (tp_rank + 1) * hq)
+    if num_kv_heads >= tp_size:
+        assert num_kv_heads % tp_size == 0
+        hkv = num_kv_heads // tp_size
+        kv_heads = range(tp_rank * hkv, (tp_rank + 1) * hkv)
+    else:
+        assert tp_size % num_kv_heads == 0
+        kv_heads = range(tp_rank // (tp_size // num_kv_heads), tp_rank // (tp_size // num_kv_heads) + 1)
+    return q_heads, kv_heads
+
+
+__all__ = ["shard_heads", "Attention", "AttentionBackend", "AttentionMetadata", "AttentionPlan", "SlotTable",
            "attention_kv_cache", "KVCachePool", "store_kvcache", "CUDAGraph", "ForwardBatch", "ForwardMode",
            "Sequence", "ops"]

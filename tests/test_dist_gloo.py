@@ -1,0 +1,62 @@
+"""CPU, world_size 2, gloo: the multi-GPU partitioning of the path.  TP shards attention by
+KV head with NO data-path collective: rank r owns Hkv/tp KV heads + their query heads and a pool holding
+only those heads, every rank sees the same page table.  Each rank runs the oracle on its shard; gathering
+the shards (test-only collective) must reproduce the unsharded result exactly, and the head partition must
+match the reference's model_runner.py:43-44 arithmetic."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import paged_attention_oracle as orc
+from tests.util import make_paged_case
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import nanovllmx_b200 as pkg
+    Hq, Hkv = 8, 4
+    case = make_paged_case([37, 5, 130], Hq, Hkv, D=64, q_lens=[37, 5, 2], seed=21)   # identical on every rank
+    hq_r, hkv_r = pkg.shard_heads(Hq, Hkv, world, rank)
+    assert len(hq_r) == Hq // world and len(hkv_r) == max(1, Hkv // world)
+    out = orc.paged_attention(case["q"][:, hq_r], case["k_cache"][:, hkv_r], case["v_cache"][:, hkv_r], case["qo_indptr"],
+                              case["kv_indptr"], case["kv_indices"], case["last_page_len"], causal=True, return_fp32=True)
+    parts = [torch.empty_like(out) for _ in range(world)]
+    dist.all_gather(parts, out.contiguous())
+    if rank == 0:
+        full = orc.paged_attention(case["q"], case["k_cache"], case["v_cache"], case["qo_indptr"], case["kv_indptr"],
+                                   case["kv_indices"], case["last_page_len"], causal=True, return_fp32=True)
+        q.put(bool(torch.equal(torch.cat(parts, dim=1), full)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_tp2_head_sharding_needs_no_collective():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    ok = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert ok and all(p.exitcode == 0 for p in procs)
+
+
+def test_shard_heads_matches_reference_arithmetic():
+    import nanovllmx_b200 as pkg
+    for Hq, Hkv in [(32, 8), (16, 8)]:
+        for tp in (1, 2, 4, 8):
+            seen_q = []
+            for r in range(tp):
+                hq, hkv = pkg.shard_heads(Hq, Hkv, tp, r)
+                assert len(hq) == Hq // tp and len(hkv) == max(1, Hkv // tp)      # model_runner.py:43-44
+                g = Hq // Hkv
+                assert all(h // g in hkv for h in hq)                              # q heads stay with their kv head
+                seen_q += list(hq)
+            assert sorted(seen_q) == list(range(Hq))
+    hq, hkv = pkg.shard_heads(16, 2, 4, 3)     # tp > Hkv: kv heads replicated (layers/linear.py:333-338)
+    assert list(hkv) == [1] and list(hq) == [12, 13, 14, 15]
