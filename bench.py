@@ -160,7 +160,8 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    Hq, Hkv, D = 32 // args.gpus, max(1, 8 // args.gpus), 128
+    # one host runs the WHOLE job's heads (the GPU arm shards them over the ranks; total work is fixed)
+    Hq, Hkv, D = 32, 8, 128
     val, dt, threads = cpu_port_gbps(args.cpu_sample_seqs, args.ctx, Hq, Hkv, D, args.page_size,
                                      steps=max(args.steps, 1), warmup=args.warmup)
     sample = f"{args.cpu_sample_seqs} of {args.batch} sequences x {args.ctx} tokens, same shapes, per step"
@@ -168,7 +169,7 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": workload_config(args, Hq, Hkv, D),
+        "config": workload_config(args, 32 // args.gpus, max(1, 8 // args.gpus), D),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -347,7 +348,7 @@ def run_b200_arm(args):
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "decode_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
+            traffic = json.load(f).get("dram_bytes_per_launch") if tp == 1 else None   # captured at TP1 shapes
     except Exception:
         pass
 

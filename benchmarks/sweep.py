@@ -55,6 +55,31 @@ def timeit(fn, iters=20, warmup=5, flush=False):
     return ts[len(ts) // 2]
 
 
+def time_graph(fn, reps=10, iters=10):
+    """GPU time per call with launch/dispatch overhead removed: `reps` calls captured in one CUDA graph."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            fn()
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        flush_l2()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); g.replay(); b.record(); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) / reps)
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
 def decode_case(B, L, Hq, Hkv, ps, ragged=False, seed=0):
     D = 128
     rng = np.random.default_rng(seed)
@@ -89,6 +114,8 @@ def bench_decode(use_fi=True):
         ms = timeit(f, flush=small)
         row = dict(case=name, B=B, L=L, Hq=Hq, Hkv=Hkv, ps=ps, MB=c["bytes"] / 1e6, ms=ms, GBs=c["bytes"] / ms / 1e6,
                    frac_measured=c["bytes"] / ms / 1e6 / PEAK)
+        if small:
+            row["graph_ms"] = time_graph(f)   # working set < L2 after the first of 10 captured calls: latency, not bandwidth
         if use_fi:
             try:
                 import flashinfer as fi
@@ -99,6 +126,8 @@ def bench_decode(use_fi=True):
                 kk, vv = c["k"].view(-1, ps, Hkv, 128), c["v"].view(-1, ps, Hkv, 128)
                 g = lambda: w.run(c["q"], (kk, vv))
                 fms = timeit(g, flush=small)
+                if small:
+                    row["flashinfer_graph_ms"] = time_graph(g)
                 row.update(flashinfer_ms=fms, flashinfer_GBs=c["bytes"] / fms / 1e6, speedup=fms / ms)
                 t0 = time.perf_counter()
                 for _ in range(20):

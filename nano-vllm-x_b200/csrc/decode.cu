@@ -34,7 +34,7 @@ constexpr int kTileBytes = kTile * kRowBytes;          // 4 KiB (K or V)
 constexpr int kStageBytes = 2 * kTileBytes;            // K + V
 constexpr int kWarpSmem = kStages * kStageBytes;       // 24 KiB
 constexpr int kDecodeSmem = kWarps * kWarpSmem;        // 192 KiB
-constexpr int kMinTilesPerCta = 8;  // do not split finer than 128 tokens per CTA
+constexpr int kMinTilesPerCta = 4;  // do not split finer than 64 tokens per CTA
 
 struct DecodeParams {
   const __nv_bfloat16* q;
@@ -44,8 +44,8 @@ struct DecodeParams {
   const int32_t* kv_indices;
   const int32_t* last_page_len;
   __nv_bfloat16* out;
-  float* part_o;      // [(G+B)*S][Hq][D]
-  float* part_lse;    // [(G+B)*S][Hq]
+  float* part_o;      // [G+B][Hq][D]
+  float* part_lse;    // [G+B][Hq]
   int32_t* seg_first; // [B]
   int32_t* seg_last;  // [B]
   int64_t q_row_stride, out_row_stride, kv_slot_stride;
@@ -140,6 +140,10 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
       if (seg_e == nt) p.seg_last[s] = slot_id;
     }
 
+    float o[kD / 8][2];
+#pragma unroll
+    for (int j = 0; j < kD / 8; ++j) o[j][0] = o[j][1] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
     if (warp_active) {
       const int page0 = p.kv_indptr[s];
       // ---- Q fragments (A operand, 16 x 128): rows >= group are zero ------------------------
@@ -156,11 +160,6 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
           qa[ks][0] = lo; qa[ks][1] = 0u; qa[ks][2] = hi; qa[ks][3] = 0u;
         }
       }
-      float o[kD / 8][2];
-#pragma unroll
-      for (int j = 0; j < kD / 8; ++j) o[j][0] = o[j][1] = 0.f;
-      float m_run = -INFINITY, l_run = 0.f;
-
       // my tiles: seg_b + sub, seg_b + sub + subs, ...
       const int n_my = (seg_e - seg_b - sub + p.subs - 1) / p.subs;  // may be <= 0
       auto tile_of = [&](int it) { return seg_b + sub + it * p.subs; };
@@ -269,25 +268,58 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
       }
       cp_async_wait<0>();
 
-      // ---- segment epilogue ----------------------------------------------------------------------
-      l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
-      l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
-      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
-      if (row_real) {
-        const int hq = kv_head * p.group + row;
-        if (whole && p.subs == 1) {
-          __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD + quad * 2;
+    }
+    // ---- segment epilogue --------------------------------------------------------------------------
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    if (p.subs > 1) {
+      // The warps that split this KV head's tile range combine inside the CTA (through their own, now
+      // idle, pipeline buffers), so a segment still yields ONE partial and whole sequences are written
+      // directly at every TP degree.
+      float* ex = reinterpret_cast<float*>(smem + warp * kWarpSmem);
+      if (warp_active && sub > 0) {
 #pragma unroll
-          for (int j = 0; j < kD / 8; ++j)
-            *reinterpret_cast<uint32_t*>(dst + j * 8) = pack_bf16x2(o[j][0] * inv_l, o[j][1] * inv_l);
-        } else {
-          const int64_t pidx = (int64_t)slot_id * p.subs + sub;
-          float* dst = p.part_o + (pidx * p.Hq + hq) * kD + quad * 2;
-#pragma unroll
-          for (int j = 0; j < kD / 8; ++j)
-            *reinterpret_cast<float2*>(dst + j * 8) = make_float2(o[j][0] * inv_l, o[j][1] * inv_l);
-          if (quad == 0) p.part_lse[pidx * p.Hq + hq] = l_run > 0.f ? m_run + fast_log2(l_run) : -INFINITY;
+        for (int j = 0; j < kD / 8; ++j)
+          *reinterpret_cast<float2*>(ex + row * kD + j * 8 + quad * 2) = make_float2(o[j][0], o[j][1]);
+        if (quad == 0) {
+          ex[8 * kD + 2 * row] = m_run;
+          ex[8 * kD + 2 * row + 1] = l_run;
         }
+      }
+      __syncthreads();
+      if (warp_active && sub == 0) {
+        for (int j2 = 1; j2 < p.subs; ++j2) {
+          const float* ox = reinterpret_cast<const float*>(smem + (hh + j2 * p.heads_per_cta) * kWarpSmem);
+          const float m2 = ox[8 * kD + 2 * row], l2 = ox[8 * kD + 2 * row + 1];
+          if (m2 == -INFINITY) continue;             // that warp had no tile in this segment
+          const float mn = fmaxf(m_run, m2);
+          const float a = fast_exp2(m_run - mn), b = fast_exp2(m2 - mn);
+#pragma unroll
+          for (int j = 0; j < kD / 8; ++j) {
+            const float2 v2 = *reinterpret_cast<const float2*>(ox + row * kD + j * 8 + quad * 2);
+            o[j][0] = o[j][0] * a + v2.x * b;
+            o[j][1] = o[j][1] * a + v2.y * b;
+          }
+          l_run = l_run * a + l2 * b;
+          m_run = mn;
+        }
+      }
+      __syncthreads();                               // buffers go back to the cp.async pipelines
+    }
+    if (warp_active && sub == 0 && row_real) {
+      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+      const int hq = kv_head * p.group + row;
+      if (whole) {
+        __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD + quad * 2;
+#pragma unroll
+        for (int j = 0; j < kD / 8; ++j)
+          *reinterpret_cast<uint32_t*>(dst + j * 8) = pack_bf16x2(o[j][0] * inv_l, o[j][1] * inv_l);
+      } else {
+        float* dst = p.part_o + ((int64_t)slot_id * p.Hq + hq) * kD + quad * 2;
+#pragma unroll
+        for (int j = 0; j < kD / 8; ++j)
+          *reinterpret_cast<float2*>(dst + j * 8) = make_float2(o[j][0] * inv_l, o[j][1] * inv_l);
+        if (quad == 0) p.part_lse[(int64_t)slot_id * p.Hq + hq] = l_run > 0.f ? m_run + fast_log2(l_run) : -INFINITY;
       }
     }
     t = pre + seg_e;
@@ -296,30 +328,56 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   }
 }
 
-// Merge pass: one CTA per (sequence, query head), one thread per output dim.
-__global__ void __launch_bounds__(kD) decode_merge_kernel(const DecodeParams p) {
-  const int s = blockIdx.x, hq = blockIdx.y, d = threadIdx.x;
-  __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD + d;
+// Merge pass: one CTA per (sequence, query head); 4 warps split the partial list, a lane owns 4 output
+// dims (float4 loads: one coalesced 512-byte row per partial per warp), warps combine through smem.
+__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
+  const int s = blockIdx.x, hq = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD;
   const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
   if (L == 0) {
-    *dst = __float2bfloat16(0.f);
+    dst[threadIdx.x] = __float2bfloat16(0.f);
     return;
   }
   const int first = p.seg_first[s], last = p.seg_last[s];
-  if (p.subs == 1 && first == last) return;  // written directly by the streaming kernel
-  const int64_t p0 = (int64_t)first * p.subs;
-  const int n = (last - first + 1) * p.subs;
+  if (first == last) return;  // one segment: written directly by the streaming kernel
+  const int n = last - first + 1;
+  const float* lse = p.part_lse + (int64_t)first * p.Hq + hq;
+  const float4* po = reinterpret_cast<const float4*>(p.part_o + ((int64_t)first * p.Hq + hq) * kD) + lane;
+  const int64_t po_stride = (int64_t)p.Hq * kD / 4;
+  __shared__ float s_m[4], s_w[4];
+  __shared__ float4 s_acc[4][32];
   float mx = -INFINITY;
-  for (int i = 0; i < n; ++i) mx = fmaxf(mx, p.part_lse[(p0 + i) * p.Hq + hq]);
-  float acc = 0.f, wsum = 0.f;
-  for (int i = 0; i < n; ++i) {
-    const float lse = p.part_lse[(p0 + i) * p.Hq + hq];
-    if (lse == -INFINITY) continue;
-    const float w = fast_exp2(lse - mx);
+  for (int i = warp; i < n; i += 4) mx = fmaxf(mx, lse[(int64_t)i * p.Hq]);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float wsum = 0.f;
+#pragma unroll 4
+  for (int i = warp; i < n; i += 4) {
+    const float l = lse[(int64_t)i * p.Hq];
+    const float w = l == -INFINITY ? 0.f : fast_exp2(l - mx);
+    const float4 v = po[(int64_t)i * po_stride];
     wsum += w;
-    acc += w * p.part_o[((p0 + i) * p.Hq + hq) * kD + d];
+    acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z; acc.w += w * v.w;
   }
-  *dst = __float2bfloat16(wsum > 0.f ? acc / wsum : 0.f);
+  if (lane == 0) { s_m[warp] = mx; s_w[warp] = wsum; }
+  s_acc[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    const float M = fmaxf(fmaxf(s_m[0], s_m[1]), fmaxf(s_m[2], s_m[3]));
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    float W = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float f = s_m[w] == -INFINITY ? 0.f : fast_exp2(s_m[w] - M);
+      const float4 a = s_acc[w][lane];
+      W += f * s_w[w];
+      r.x += f * a.x; r.y += f * a.y; r.z += f * a.z; r.w += f * a.w;
+    }
+    const float inv = W > 0.f ? 1.f / W : 0.f;
+    uint2 o2;
+    o2.x = pack_bf16x2(r.x * inv, r.y * inv);
+    o2.y = pack_bf16x2(r.z * inv, r.w * inv);
+    *reinterpret_cast<uint2*>(dst + lane * 4) = o2;
+  }
 }
 
 static int ilog2_exact_d(int x) {
@@ -350,7 +408,7 @@ extern "C" size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv
   DecodeCfg c;
   if (B <= 0 || Hq <= 0 || D <= 0 || !decode_cfg(Hkv, &c)) return 0;
   const int G = cached_num_sms();
-  const size_t parts = (size_t)(G + B) * c.subs;
+  const size_t parts = (size_t)(G + B);
   size_t bytes = parts * Hq * D * sizeof(float);       // part_o
   bytes += parts * Hq * sizeof(float);                 // part_lse
   bytes += 2 * (size_t)B * sizeof(int32_t);            // seg_first / seg_last
@@ -378,8 +436,8 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
     return fail("b200_decode: null pointer");
   if (((uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)workspace) & 15 || (kv_slot_stride & 7))
     return fail("b200_decode: k_cache / v_cache / workspace must be 16-byte aligned");
-  if (((uintptr_t)q | (uintptr_t)out) & 3 || (q_row_stride & 1) || (out_row_stride & 1))
-    return fail("b200_decode: q / out must be 4-byte aligned");
+  if (((uintptr_t)q & 3) || (q_row_stride & 1)) return fail("b200_decode: q must be 4-byte aligned");
+  if (((uintptr_t)out & 7) || (out_row_stride & 3)) return fail("b200_decode: out must be 8-byte aligned");
   const size_t need = b200_decode_workspace_bytes(B, Hq, Hkv, D);
   if (workspace_bytes < need) return fail("b200_decode: workspace %zu < %zu bytes", workspace_bytes, need);
 
@@ -392,7 +450,7 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   p.kv_indices = kv_indices;
   p.last_page_len = last_page_len;
   p.out = (__nv_bfloat16*)out;
-  const size_t parts = (size_t)(G + B) * c.subs;
+  const size_t parts = (size_t)(G + B);
   p.part_o = (float*)workspace;
   p.part_lse = p.part_o + parts * Hq * D;
   p.seg_first = (int32_t*)(p.part_lse + parts * Hq);
@@ -414,6 +472,6 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   cudaStream_t st = (cudaStream_t)stream;
   decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
   if (int rc = check_launch("b200_decode(stream)")) return rc;
-  decode_merge_kernel<<<dim3(B, Hq), kD, 0, st>>>(p);
+  decode_merge_kernel<<<dim3(B, Hq), 128, 0, st>>>(p);
   return check_launch("b200_decode(merge)");
 }

@@ -154,46 +154,46 @@ class SlotTable:
                 max_len = n
         if max_len > self.table.shape[1]:
             self._grow(self.table.shape[0], max(max_len, 2 * self.table.shape[1]))
-        hdr = np.empty((7, B), dtype=np.int32)
+        rows, kvl, cach, qls, wcol, wcnt, woff = [], [], [], [], [], [], []
         payload: list = []
         total_q = total_kv = total_new = 0
-        unknown = sum(1 for s in seqs if s.seq_id not in self.row_of)
-        for i, s in enumerate(seqs):
+        row_of, tracked, last_used, step = self.row_of, self.tracked_len, self.last_used, self.step
+        unknown = -1
+        for s in seqs:
             kv = s.kv_indices
             n = len(kv)
             cached = s.cached_kv_len
-            row = self.row_of.get(s.seq_id)
+            row = row_of.get(s.seq_id)
             if row is None:
+                if unknown < 0:
+                    unknown = sum(1 for x in seqs if x.seq_id not in row_of)
                 row = self._take_row(unknown)
-                self.row_of[s.seq_id] = row
+                tracked, last_used = self.tracked_len, self.last_used     # _take_row may have grown them
+                row_of[s.seq_id] = row
                 self.owner[row] = s.seq_id
                 start = 0
             else:
-                start = min(self.tracked_len[row], cached)
+                t = tracked[row]
+                start = t if t < cached else cached
             if self.verify:
                 mir = self._mirror.get(s.seq_id, [])
                 assert mir[:start] == list(kv[:start]), f"slot table contract violated for seq {s.seq_id}"
                 self._mirror[s.seq_id] = list(kv)
-            self.last_used[row] = self.step
+            last_used[row] = step
             cnt = n - start if n > start else 0
-            hdr[0, i] = row
-            hdr[1, i] = n
-            hdr[2, i] = cached
             q = len(s.token_ids) - cached
-            hdr[3, i] = q
-            hdr[4, i] = start
-            hdr[5, i] = cnt
-            hdr[6, i] = len(payload)
-            if cnt:
+            rows.append(row); kvl.append(n); cach.append(cached); qls.append(q)
+            wcol.append(start); wcnt.append(cnt); woff.append(len(payload))
+            if cnt == 1:
+                payload.append(kv[-1])
+            elif cnt:
                 payload.extend(kv[start:] if start else kv)
-            self.tracked_len[row] = n
+            tracked[row] = n
             total_q += q
             total_kv += n
-            total_new += n - cached if n > cached else 0
-        msg = np.empty(7 * B + len(payload), dtype=np.int32)
-        msg[:7 * B] = hdr.reshape(-1)
-        if payload:
-            msg[7 * B:] = payload
+            if n > cached:
+                total_new += n - cached
+        msg = np.array(rows + kvl + cach + qls + wcol + wcnt + woff + payload, dtype=np.int32)
         host = torch.from_numpy(msg)
         if self.device.type == "cuda":
             host = host.pin_memory()
