@@ -79,6 +79,59 @@ __global__ void __launch_bounds__(256) store_kv_kernel(const char* __restrict__ 
   }
 }
 
+// Row-cooperative variant for the common row sizes: LANES threads own one (token, K|V) row, each moves VPL
+// 16-byte vectors of it, and ROWS rows are in flight per thread group (VPL*ROWS == 4 independent loads before
+// the first store).  No integer division on the hot path (the flat kernel above needs a 64-bit div per item).
+template <int LANES, int VPL, int ROWS>
+__global__ void __launch_bounds__(256) store_kv_rows_kernel(const char* __restrict__ k, int64_t k_row_bytes,
+                                                            const char* __restrict__ v, int64_t v_row_bytes,
+                                                            char* __restrict__ k_cache, char* __restrict__ v_cache,
+                                                            const int64_t* __restrict__ slots, int T,
+                                                            int64_t cache_row_bytes) {
+  const int lane = threadIdx.x % LANES;
+  const int groups = (gridDim.x * blockDim.x) / LANES;
+  const int total_rows = 2 * T;
+  for (int row0 = (blockIdx.x * blockDim.x + threadIdx.x) / LANES; row0 < total_rows; row0 += groups * ROWS) {
+    int4 val[ROWS][VPL];
+    char* dst[ROWS];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const int row = row0 + r * groups;
+      dst[r] = nullptr;
+      if (row < total_rows) {
+        const bool is_v = row >= T;
+        const int t = is_v ? row - T : row;
+        const int64_t slot = __ldg(slots + t);
+        if (slot >= 0) {
+          const char* src = (is_v ? v + t * v_row_bytes : k + t * k_row_bytes) + lane * 16;
+#pragma unroll
+          for (int c = 0; c < VPL; ++c) val[r][c] = VecIO<int4>::ld(src + c * LANES * 16);
+          dst[r] = (is_v ? v_cache : k_cache) + slot * cache_row_bytes + lane * 16;
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r)
+      if (dst[r]) {
+#pragma unroll
+        for (int c = 0; c < VPL; ++c) VecIO<int4>::st(dst[r] + c * LANES * 16, val[r][c]);
+      }
+  }
+}
+
+template <int LANES, int VPL, int ROWS>
+static int launch_store_rows(const void* k, int64_t kb, const void* v, int64_t vb, void* k_cache, void* v_cache,
+                             const int64_t* slots, int T, int64_t row_bytes, cudaStream_t st) {
+  const int64_t groups_needed = (2ll * T + ROWS - 1) / ROWS;
+  int64_t blocks = (groups_needed * LANES + 255) / 256;
+  const int64_t cap = (int64_t)cached_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  store_kv_rows_kernel<LANES, VPL, ROWS><<<(unsigned)blocks, 256, 0, st>>>(
+      (const char*)k, kb, (const char*)v, vb, (char*)k_cache, (char*)v_cache, slots, T, row_bytes);
+  return check_launch("b200_store_kv");
+}
+
 template <typename V>
 static int launch_store(const void* k, int64_t k_row_bytes, const void* v, int64_t v_row_bytes, void* k_cache,
                         void* v_cache, const int64_t* slots, int T, int64_t row_bytes, cudaStream_t st) {
@@ -115,7 +168,15 @@ extern "C" int b200_store_kv(const void* k, int64_t k_row_stride, const void* v,
   cudaStream_t st = (cudaStream_t)stream;
   const uintptr_t align_or = (uintptr_t)k | (uintptr_t)v | (uintptr_t)k_cache | (uintptr_t)v_cache |
                              (uintptr_t)row_bytes | (uintptr_t)kb | (uintptr_t)vb;
-  if ((align_or & 15) == 0) return launch_store<int4>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
+  if ((align_or & 15) == 0) {
+    switch (row_bytes) {   // Hkv_local * 128 * 2 B: 2 KiB (8 heads) ... 256 B (1 head)
+      case 2048: return launch_store_rows<32, 4, 1>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
+      case 1024: return launch_store_rows<32, 2, 2>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
+      case 512: return launch_store_rows<32, 1, 4>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
+      case 256: return launch_store_rows<16, 1, 4>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
+      default: return launch_store<int4>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
+    }
+  }
   if ((align_or & 7) == 0) return launch_store<int2>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
   if ((align_or & 3) == 0) return launch_store<int>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);
   if ((align_or & 1) == 0) return launch_store<short>(k, kb, v, vb, k_cache, v_cache, slots, T, row_bytes, st);

@@ -146,14 +146,7 @@ class SlotTable:
     def pack_step(self, seqs) -> tuple[torch.Tensor, int, int, int, int]:
         """Returns (device message, n_payload, total_q, total_pages_at_ps1, total_new)."""
         self.step += 1
-        B = len(seqs)
         max_len = 0
-        for s in seqs:
-            n = len(s.kv_indices)
-            if n > max_len:
-                max_len = n
-        if max_len > self.table.shape[1]:
-            self._grow(self.table.shape[0], max(max_len, 2 * self.table.shape[1]))
         rows, kvl, cach, qls, wcol, wcnt, woff = [], [], [], [], [], [], []
         payload: list = []
         total_q = total_kv = total_new = 0
@@ -189,10 +182,14 @@ class SlotTable:
             elif cnt:
                 payload.extend(kv[start:] if start else kv)
             tracked[row] = n
+            if n > max_len:
+                max_len = n
             total_q += q
             total_kv += n
             if n > cached:
                 total_new += n - cached
+        if max_len > self.table.shape[1]:      # (the copy of the old contents is ordered before this step's update)
+            self._grow(self.table.shape[0], max(max_len, 2 * self.table.shape[1]))
         msg = np.array(rows + kvl + cach + qls + wcol + wcnt + woff + payload, dtype=np.int32)
         host = torch.from_numpy(msg)
         if self.device.type == "cuda":
@@ -248,7 +245,6 @@ class AttentionBackend:
         mode = mode_name(batch.forward_mode)
         st = self.slot_table
         msg, n_payload, total_q, total_kv, total_new = st.pack_step(seqs)
-        ops.slot_table_update(st.table, msg, B, n_payload)
         ps = self.page_size
         if ps == 1:
             n_pages = total_kv
@@ -262,8 +258,8 @@ class AttentionBackend:
         out_slots = torch.empty(total_new, dtype=torch.int64, device=dev)
         scratch = torch.empty(B + 1, dtype=torch.int32, device=dev)
         if B > 0:
-            ops.build_meta(st.table, msg, B, B, ps, False, qo_indptr, kv_indptr, kv_indices, last_page_len,
-                           out_slots, scratch)
+            ops.step_meta(st.table, msg, B, n_payload, B, ps, False, qo_indptr, kv_indptr, kv_indices, last_page_len,
+                          out_slots, scratch)
         else:
             qo_indptr.zero_()
             kv_indptr.zero_()
@@ -314,15 +310,14 @@ class AttentionBackend:
         bs = len(seqs)
         st = self.slot_table
         msg, n_payload, _tq, total_kv, _tn = st.pack_step(seqs)
-        ops.slot_table_update(st.table, msg, bs, n_payload)
         indptr_buf = graph.get_input_buffer("paged_kv_indptr_buffer")
         indices_buf = graph.get_input_buffer("paged_kv_indices_buffer")
         last_buf = graph.get_input_buffer("paged_kv_last_page_len_buffer")
         out_buf = graph.get_input_buffer("output_kv_indices_buffer")
         # the reference never rewrites last_page_len on replay (stays 1 at page_size 1); for
         # page_size > 1 it must be rebuilt
-        ops.build_meta(st.table, msg, bs, padded_bs, self.page_size, True, None, indptr_buf, indices_buf,
-                       None if self.page_size == 1 else last_buf, out_buf, self._graph_scratch)
+        ops.step_meta(st.table, msg, bs, n_payload, padded_bs, self.page_size, True, None, indptr_buf, indices_buf,
+                      None if self.page_size == 1 else last_buf, out_buf, self._graph_scratch)
         plan = self._graph_plans[padded_bs]
         return AttentionMetadata(forward_mode=batch.forward_mode, kv_cache=self.kv_cache,
                                  output_kv_indices=out_buf[:padded_bs], wrapper=plan)

@@ -85,6 +85,29 @@ def build_meta(slot_table: torch.Tensor, step_msg: torch.Tensor, B: int, padded_
     _lib.check(rc, "b200_build_meta")
 
 
+
+@torch.library.custom_op("b200attn::step_meta",
+                         mutates_args=("slot_table", "qo_indptr", "kv_indptr", "kv_indices", "last_page_len",
+                                       "out_slots", "scratch"),
+                         device_types="cuda")
+def step_meta(slot_table: torch.Tensor, step_msg: torch.Tensor, B: int, n_payload: int, padded_bs: int,
+              page_size: int, fill_tail: bool, qo_indptr: torch.Tensor | None, kv_indptr: torch.Tensor,
+              kv_indices: torch.Tensor, last_page_len: torch.Tensor | None, out_slots: torch.Tensor,
+              scratch: torch.Tensor) -> None:
+    """slot_table_update + build_meta behind ONE dispatcher round trip (the per-step host cost of the
+    metadata path is dominated by Python/dispatcher overhead, not by the three tiny kernels)."""
+    _need_cuda(slot_table, step_msg, kv_indptr, kv_indices, out_slots, scratch)
+    lib = _lib.load()
+    st = _stream()
+    if B > 0 and n_payload > 0:
+        _lib.check(lib.b200_slot_table_update(slot_table.data_ptr(), slot_table.stride(0), step_msg.data_ptr(), B,
+                                              n_payload, st), "b200_slot_table_update")
+    _lib.check(lib.b200_build_meta(slot_table.data_ptr(), slot_table.stride(0), step_msg.data_ptr(), B, padded_bs,
+                                   page_size, int(fill_tail), _ptr(qo_indptr), kv_indptr.data_ptr(),
+                                   kv_indices.data_ptr(), kv_indices.numel(), _ptr(last_page_len),
+                                   out_slots.data_ptr(), out_slots.numel(), scratch.data_ptr(), st), "b200_build_meta")
+
+
 # ---- (3) decode -------------------------------------------------------------------------------------
 def decode_workspace_bytes(B: int, Hq: int, Hkv: int, D: int) -> int:
     return int(_lib.load().b200_decode_workspace_bytes(B, Hq, Hkv, D))

@@ -36,7 +36,7 @@ def test_loader_and_error_path(pkg):
 def test_ops_registered_and_no_cpu_fallback(pkg):
     import pytest
     import torch
-    for name in ("store_kv", "slot_table_update", "build_meta", "decode", "prefill"):
+    for name in ("store_kv", "slot_table_update", "build_meta", "step_meta", "decode", "prefill"):
         assert hasattr(torch.ops.b200attn, name)
     k = torch.zeros(2, 1, 8, dtype=torch.bfloat16)
     with pytest.raises(Exception):
