@@ -421,8 +421,13 @@ def main():
         print(json.dumps(res), flush=True)
         if a.dump_tokens:
             json.dump(out_tokens, open(a.dump_tokens, "w"))
+    sys.stdout.flush()
     if world > 1:
-        dist.destroy_process_group()
+        # NCCL kernels live inside the captured CUDA graphs: destroy_process_group() with those graphs alive hangs
+        # until the watchdog aborts (16 min).  Everything is printed; leave without the teardown.
+        torch.cuda.synchronize()
+        dist.barrier()
+        os._exit(0)
 
 
 from contextlib import contextmanager

@@ -16,7 +16,7 @@ if what.startswith("prefill"):
     else:
         pl = [len(p) for p in bench_workload()[0]][:64]
         c = prefill_case(pl, [0] * 64, 32, 8)
-    ws = torch.empty(256, dtype=torch.uint8, device=DEV)
+    ws = torch.empty(pkg.ops.prefill_workspace_bytes(c["B"], c["T"], 32, 8, 128), dtype=torch.uint8, device=DEV)
     f = lambda: pkg.ops.prefill(c["q"], c["k"], c["v"], c["qo"], c["indptr"], c["idx"], c["last"], ws, 1, 128 ** -0.5, True)
 else:
     c = decode_case(64, 32768, 4, 1, 16) if what == "decode_tp8" else decode_case(256, 2048, 16, 8, 1, True)

@@ -38,20 +38,26 @@ def flush_l2():
 
 
 def timeit(fn, iters=20, warmup=5, flush=False):
+    """Median GPU time of one call.  All iterations are enqueued before the single sync, so the GPU never
+    waits for the Python dispatch of the next call (an event pair around a call issued to an IDLE GPU also
+    measures the host's launch latency, ~45 us through torch.library + ctypes)."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
-    ts = []
+    evs = []
+    if not flush:
+        fn()                                     # keeps the queue non-empty ahead of the first timed call
     for _ in range(iters):
         if flush:
+            torch.cuda._sleep(300000)            # ~150 us of GPU time: lets the host enqueue the timed call first
             flush_l2()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         fn()
         b.record()
-        torch.cuda.synchronize()
-        ts.append(a.elapsed_time(b))
-    ts.sort()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in evs)
     return ts[len(ts) // 2]
 
 

@@ -134,7 +134,11 @@ int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const 
  *     <= Lkv - Lq + j.  K/V of the new tokens must already be in the pool (b200_store_kv).
  *
  *     q, out      : [T, Hq, D]; qo_indptr int32 [B+1]; total_q = T (host-known upper bound of
- *                   qo_indptr[B]; sizes the grid, no device sync)
+ *                   qo_indptr[B]; sizes the work list, no device sync)
+ *     workspace   : >= b200_prefill_workspace_bytes(B, total_q, Hq, Hkv, D) bytes, 16-byte aligned.
+ *                   Holds the device-built work list (one (sequence, query tile) pair per 256 packed
+ *                   query rows, heaviest first) and the counter the persistent CTAs draw from; a
+ *                   short workspace is an error (no fallback).
  * ---------------------------------------------------------------------------------------- */
 size_t b200_prefill_workspace_bytes(int32_t B, int32_t total_q, int32_t Hq, int32_t Hkv, int32_t D);
 

@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = gridDim.x;
   const int head_group = blockIdx.y;  // which block of heads_per_cta KV heads
+  griddep_launch_dependents();        // the merge grid may become resident now; it waits for this grid to finish
 
   // ---- device-side schedule: total tiles, this CTA's range, first sequence ------------------
   int total;
@@ -333,6 +334,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
 __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
   const int s = blockIdx.x, hq = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD;
+  griddep_wait();                     // launched with PDL: partials / segment maps come from decode_kernel
   const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
   if (L == 0) {
     dst[threadIdx.x] = __float2bfloat16(0.f);
@@ -472,6 +474,7 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   cudaStream_t st = (cudaStream_t)stream;
   decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
   if (int rc = check_launch("b200_decode(stream)")) return rc;
-  decode_merge_kernel<<<dim3(B, Hq), 128, 0, st>>>(p);
+  cudaError_t e = launch_pdl(decode_merge_kernel, dim3(B, Hq), dim3(128), 0, st, p);
+  if (e != cudaSuccess) return fail("b200_decode(merge): %s", cudaGetErrorString(e));
   return check_launch("b200_decode(merge)");
 }

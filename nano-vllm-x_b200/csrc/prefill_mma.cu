@@ -251,8 +251,12 @@ int launch_prefill_mma(const PrefillParams& p, int total_q, cudaStream_t st) {
 }  // namespace b200
 
 extern "C" size_t b200_prefill_workspace_bytes(int32_t B, int32_t total_q, int32_t Hq, int32_t Hkv, int32_t D) {
-  (void)B; (void)total_q; (void)Hq; (void)Hkv; (void)D;
-  return 256;  // the mma path needs none; keep a non-zero size so callers can always pass a pointer
+  (void)D;
+  if (B <= 0 || total_q <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return 256;
+  // work list of the persistent tcgen05 kernel (the mma.sync fallback needs none); never zero so that
+  // callers can always pass a pointer
+  const size_t need = b200::prefill_sm100_supports(Hq / Hkv) ? b200::prefill_sm100_workspace_bytes(B, total_q, Hq / Hkv) : 0;
+  return (need + 255) & ~(size_t)255 ? ((need + 255) & ~(size_t)255) : 256;
 }
 
 extern "C" int b200_prefill(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
@@ -262,7 +266,6 @@ extern "C" int b200_prefill(const void* q, int64_t q_row_stride, const void* k_c
                             int32_t total_q, int32_t Hq, int32_t Hkv, int32_t D, int32_t page_size, float sm_scale,
                             int32_t causal, int32_t dtype, b200_stream_t stream) {
   using namespace b200;
-  (void)workspace; (void)workspace_bytes;
   if (B < 0 || total_q < 0) return fail("b200_prefill: negative size");
   if (B == 0 || total_q == 0) return 0;
   if (D != kPD) return fail("b200_prefill: head_dim %d not built (round 1 builds D=128)", D);
@@ -292,6 +295,6 @@ extern "C" int b200_prefill(const void* q, int64_t q_row_stride, const void* k_c
   // tcgen05/TMEM kernel for every shape it covers; the mma.sync kernel only for GQA groups that do
   // not pack into a 128-row tile.  B200ATTN_PREFILL=mma forces the latter (A/B measurements only).
   static const bool force_mma = [] { const char* e = getenv("B200ATTN_PREFILL"); return e && e[0] == 'm'; }();
-  if (!force_mma && prefill_sm100_supports(p.group)) return launch_prefill_sm100(p, total_q, (cudaStream_t)stream);
+  if (!force_mma && prefill_sm100_supports(p.group)) return launch_prefill_sm100(p, total_q, workspace, workspace_bytes, (cudaStream_t)stream);
   return launch_prefill_mma(p, total_q, (cudaStream_t)stream);
 }

@@ -18,6 +18,7 @@ struct PrefillParams {
   float scale_log2;
 };
 int launch_prefill_mma(const PrefillParams& p, int total_q, cudaStream_t st);
-int launch_prefill_sm100(const PrefillParams& p, int total_q, cudaStream_t st);
+int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, size_t workspace_bytes, cudaStream_t st);
+size_t prefill_sm100_workspace_bytes(int B, int total_q, int group);
 bool prefill_sm100_supports(int group);
 }  // namespace b200

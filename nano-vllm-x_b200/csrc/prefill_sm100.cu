@@ -690,31 +690,513 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const P
   if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
-int launch_prefill_sm100(const PrefillParams& p, int total_q, cudaStream_t st) {
+// =====================================================================================================
+// Stage 3: the same warp-specialised pipeline made PERSISTENT (the production path).
+//
+// One CTA per SM walks a device-built work list instead of paying launch prologue + pipeline ramp
+// per 256-row tile (bench-shaped prompts are 100..1024 tokens: a tile owns only 1..8 KV tiles, so the
+// per-CTA fixed cost was ~2/3 of the run time).
+//   * prefill_plan_kernel (1 CTA) lists every (sequence, 256-row query tile) pair, counting-sorted
+//     by its number of KV tiles, heaviest first, and zeroes the work counter.
+//   * warp 11 of every CTA is the scheduler: atomicAdd on the counter, (pair, kv head) -> geometry,
+//     published one item AHEAD through a 4-entry shared-memory ring (mbarrier full/empty), so
+//     the heaviest items start first and the tail is made of the lightest (LPT, dynamic).
+//   * loaders, MMA issuer and softmax groups each run their own item loop with running mbarrier
+//     phases; the loaders prefetch the next item's Q and K/V while the softmax groups are still in
+//     the current item's last tile and epilogue (Q buffer hand-over: tcgen05.commit -> bar_qfree).
+//   * TMEM hazards across items need no extra barrier: QK_t(0) of the next item is issued after
+//     PV_t(last) on the in-order MMA pipe, and PV_t(0) waits for P_t(0), which group t only
+//     produces after its epilogue has read O_t out (tcgen05.wait::ld precedes the arrive).
+// =====================================================================================================
+constexpr int kItemRing = 4;
+constexpr int kPlanThreads = 1024;
+constexpr int kPlanBuckets = 1024;
+constexpr int kWorkHeaderInts = 16;     // [0] work counter, [1] number of (sequence, tile) pairs
+
+struct ItemDesc {
+  int s, kvh, j0, Lq, Lkv, q0, page0, valid;
+};
+
+struct ItemGeo {
+  int toks0, toks1, kvhi0, kvhi1, nt0, nt1, J, kv_hi_all;
+};
+
+__device__ __forceinline__ ItemGeo item_geometry(const ItemDesc& d, const int tok_per_tile, const int causal) {
+  ItemGeo g;
+  g.toks0 = max(0, min(tok_per_tile, d.Lq - d.j0));
+  g.toks1 = max(0, min(tok_per_tile, d.Lq - d.j0 - tok_per_tile));
+  g.kvhi0 = causal ? min(d.Lkv, d.Lkv - d.Lq + d.j0 + g.toks0) : d.Lkv;
+  g.kvhi1 = causal ? min(d.Lkv, d.Lkv - d.Lq + d.j0 + tok_per_tile + g.toks1) : d.Lkv;
+  if (g.kvhi0 < 0 || g.toks0 == 0) g.kvhi0 = 0;
+  if (g.kvhi1 < 0 || g.toks1 == 0) g.kvhi1 = 0;
+  g.nt0 = (g.kvhi0 + kTN - 1) / kTN;
+  g.nt1 = (g.kvhi1 + kTN - 1) / kTN;
+  g.J = max(g.nt0, g.nt1);
+  g.kv_hi_all = max(g.kvhi0, g.kvhi1);
+  return g;
+}
+
+// Work list for the persistent kernel: pairs (sequence, query tile) bucketed by KV-tile count, heaviest
+// bucket first.  Order inside a bucket is arbitrary (atomics): it only affects scheduling, every item
+// is computed independently, so results do not depend on it.
+__global__ void __launch_bounds__(kPlanThreads, 1) prefill_plan_kernel(const PrefillParams p, const int tok_per_cta,
+                                                                        int* __restrict__ work, int2* __restrict__ items,
+                                                                        const int max_pairs) {
+  __shared__ int s_hist[kPlanBuckets];
+  __shared__ int s_scan[kPlanThreads / 32 + 1];
+  const int tid = threadIdx.x;
+  griddep_launch_dependents();   // the persistent grid may set up (barriers, TMEM) while the list is built
+  s_hist[tid] = 0;
+  __syncthreads();
+  auto tiles_of_pair = [&](int Lq, int Lkv, int qt) {
+    const int j0 = qt * tok_per_cta;
+    int hi = p.causal ? min(Lkv, Lkv - Lq + min(Lq, j0 + tok_per_cta)) : Lkv;
+    hi = max(hi, 0);
+    return min((hi + kTN - 1) / kTN, kPlanBuckets - 1);
+  };
+  for (int i = tid; i < p.B; i += kPlanThreads) {
+    const int Lq = p.qo_indptr[i + 1] - p.qo_indptr[i];
+    const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps);
+    const int nq = (Lq + tok_per_cta - 1) / tok_per_cta;
+    for (int qt = 0; qt < nq; ++qt) atomicAdd(&s_hist[tiles_of_pair(Lq, Lkv, qt)], 1);
+  }
+  __syncthreads();
+  // thread t owns bucket (kPlanBuckets - 1 - t): an inclusive scan in thread order is a scan heaviest-first
+  const int mine = s_hist[kPlanBuckets - 1 - tid];
+  int total;
+  const int incl = block_inclusive_scan<kPlanThreads>(mine, s_scan, &total);
+  __syncthreads();
+  s_hist[kPlanBuckets - 1 - tid] = incl - mine;   // start offset of my bucket
+  __syncthreads();
+  for (int i = tid; i < p.B; i += kPlanThreads) {
+    const int Lq = p.qo_indptr[i + 1] - p.qo_indptr[i];
+    const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps);
+    const int nq = (Lq + tok_per_cta - 1) / tok_per_cta;
+    for (int qt = 0; qt < nq; ++qt) {
+      const int pos = atomicAdd(&s_hist[tiles_of_pair(Lq, Lkv, qt)], 1);
+      if (pos < max_pairs) items[pos] = make_int2(i, qt);
+    }
+  }
+  if (tid == 0) {
+    work[0] = 0;
+    work[1] = min(total, max_pairs);
+  }
+}
+
+__global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(const PrefillParams p, const int log2_g,
+                                                                               int* __restrict__ work,
+                                                                               const int2* __restrict__ items) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t s_tmem;
+  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing];
+  __shared__ __align__(16) int s_slots[2][2][2][32];   // [tile parity][loader warp][row parity][i]
+  __shared__ __align__(16) ItemDesc s_items[kItemRing];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int G = 1 << log2_g;
+  const int tok_per_tile = kTM >> log2_g;
+  const int tok_per_cta = 2 * tok_per_tile;
+
+  const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar0 = smem_u32(&s_bar[0]);
+  const uint32_t bar_q = bar0, bar_qfree = bar0 + 8u;
+  auto bar_full = [&](int slot) { return bar0 + 8u * (2 + slot); };
+  auto bar_empty = [&](int slot) { return bar0 + 8u * (2 + kRing + slot); };
+  auto bar_s = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + t); };
+  auto bar_p = [&](int t, int half) { return bar0 + 8u * (2 + 2 * kRing + 2 + 2 * t + half); };
+  auto bar_o = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 6 + t); };
+  auto bar_ifull = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + slot); };
+  auto bar_iempty = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + kItemRing + slot); };
+  constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 loader warps (lane 0 of each arrives)
+
+  if (tid == 0) {
+    mbar_init(bar_q, kWsLoaders);
+    mbar_init(bar_qfree, 1);
+    for (int i = 0; i < kRing; ++i) {
+      mbar_init(bar_full(i), kWsLoaders);
+      mbar_init(bar_empty(i), 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(bar_s(t), 1);
+      mbar_init(bar_p(t, 0), 128);
+      mbar_init(bar_p(t, 1), 128);
+      mbar_init(bar_o(t), 1);
+    }
+    for (int i = 0; i < kItemRing; ++i) {
+      mbar_init(bar_ifull(i), 1);
+      mbar_init(bar_iempty(i), kItemConsumers);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&s_tmem), 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+
+  // every consumer warp: wait for item `it`, copy it to registers, release the ring entry
+  auto take_item = [&](int it) -> ItemDesc {
+    const int islot = it % kItemRing;
+    mbar_wait(bar_ifull(islot), (it / kItemRing) & 1);
+    const ItemDesc d = s_items[islot];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_iempty(islot));
+    return d;
+  };
+
+  if (warp == 11) {
+    // =================================== scheduler =========================================================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+    griddep_wait();                // launched with PDL: the work list comes from prefill_plan_kernel
+    const int n_total = work[1] * p.Hkv;
+    for (int it = 0;; ++it) {
+      const int islot = it % kItemRing;
+      mbar_wait(bar_iempty(islot), ((it / kItemRing) & 1) ^ 1);
+      int valid = 0;
+      if (lane == 0) {
+        ItemDesc d;
+        const int w = atomicAdd(&work[0], 1);
+        d.valid = w < n_total ? 1 : 0;
+        d.s = d.kvh = d.j0 = d.Lq = d.Lkv = d.q0 = d.page0 = 0;
+        if (d.valid) {
+          const int pair = w / p.Hkv;
+          const int2 sq = items[pair];
+          d.s = sq.x;
+          d.kvh = w - pair * p.Hkv;
+          d.j0 = sq.y * tok_per_cta;
+          d.q0 = p.qo_indptr[sq.x];
+          d.Lq = p.qo_indptr[sq.x + 1] - d.q0;
+          d.Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, sq.x, p.log2_ps);
+          d.page0 = p.kv_indptr[sq.x];
+        }
+        s_items[islot] = d;
+        mbar_arrive(bar_ifull(islot));
+        valid = d.valid;
+      }
+      valid = __shfl_sync(0xffffffffu, valid, 0);
+      if (!valid) break;
+    }
+  } else if (warp >= 9) {
+    // =================================== loaders ==========================================================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+    const int lt = tid - 9 * 32;                    // 0..63
+    const int gc = lt & 15, lrow0 = lt >> 4;        // rows lrow0 + 4*i
+    const uint32_t chunk_off = (uint32_t)(gc >> 3) * kBlkBytes;
+    const int c8 = gc & 7;
+    const int ps_mask = (1 << p.log2_ps) - 1;
+    const int lw = warp - 9;
+    const int hrow = lane >> 4;
+    const uint32_t stride_b = (uint32_t)(p.kv_slot_stride * 2);   // bytes between token slots (< 4 GiB)
+    const uint32_t dst_even = chunk_off + lrow0 * 128 + ((c8 ^ lrow0) << 4);
+    const uint32_t dst_odd = chunk_off + lrow0 * 128 + ((c8 ^ (lrow0 + 4)) << 4);
+    // One cp.async group per fill (Q, K(0), V(0), K(1), ...).  A fill's mbarrier is signalled when the NEXT
+    // fill has been issued (wait_group 1), so one fill is always in flight; before blocking on anything
+    // that may depend on the consumers, the pending fill is flushed.
+    uint32_t pend_bar = 0;
+    auto rotate = [&](uint32_t this_bar) {
+      cp_async_commit();
+      cp_async_wait<1>();
+      fence_proxy_async_smem();
+      if (pend_bar) mbar_arrive(pend_bar);
+      pend_bar = this_bar;
+    };
+    auto flush = [&]() {
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      if (pend_bar) mbar_arrive(pend_bar);
+      pend_bar = 0;
+    };
+    auto wait_or_flush = [&](uint32_t bar, uint32_t parity) {
+      if (!mbar_try_wait(bar, parity)) {
+        flush();
+        mbar_wait(bar, parity);
+      }
+    };
+    int fill = 0, qn = 0;
+    int sl[32];
+    for (int it = 0;; ++it) {
+      {
+        const int islot = it % kItemRing;
+        wait_or_flush(bar_ifull(islot), (it / kItemRing) & 1);
+      }
+      const ItemDesc d = take_item(it);
+      if (!d.valid) break;
+      const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
+      if (g.J == 0) continue;
+      const int kvh = d.kvh;
+      // ---- Q: 256 packed rows ------------------------------------------------------------------------------
+      wait_or_flush(bar_qfree, (qn & 1) ^ 1);
+      {
+        const int rows_total = (g.toks0 + g.toks1) << log2_g;
+#pragma unroll 4
+        for (int i = 0; i < 256 / 4; ++i) {
+          const int R = lrow0 + 4 * i;                  // packed row 0..255
+          const bool ok = R < rows_total;
+          const int tok = d.j0 + (R >> log2_g), head = kvh * G + (R & (G - 1));
+          const __nv_bfloat16* src = p.q + (int64_t)(d.q0 + (ok ? tok : d.j0)) * p.q_row_stride +
+                                     (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
+          const int r = R & 127;
+          cp_async_16(smem + kWsOffQ + (R >> 7) * kTileBytes2 + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src,
+                      ok ? 16u : 0u);
+        }
+      }
+      rotate(bar_q);
+      ++qn;
+      auto fetch_slots = [&](int tile) {
+        const int tok = tile * kTN + 4 * lane + 2 * lw;
+        int sa = -1, sb = -1;
+        if (tok < g.kv_hi_all) {
+          const int page = __ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps));
+          sa = (page << p.log2_ps) + (tok & ps_mask);
+        }
+        if (tok + 1 < g.kv_hi_all) {
+          const int page = __ldg(p.kv_indices + d.page0 + ((tok + 1) >> p.log2_ps));
+          sb = (page << p.log2_ps) + ((tok + 1) & ps_mask);
+        }
+        s_slots[tile & 1][lw][0][lane] = sa;
+        s_slots[tile & 1][lw][1][lane] = sb;
+      };
+      fetch_slots(0);
+      const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)kvh * kTD + gc * 8);
+      const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)kvh * kTD + gc * 8);
+      const int N = 2 * g.J;
+      for (int n = 0; n < N; ++n, ++fill) {
+        const int slot = fill % kRing, use = fill / kRing;
+        const int tile = n >> 1;
+        if ((n & 1) == 0) {
+          __syncwarp();
+          const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int4 v = src[i];
+            sl[4 * i] = v.x; sl[4 * i + 1] = v.y; sl[4 * i + 2] = v.z; sl[4 * i + 3] = v.w;
+          }
+          __syncwarp();
+          if (tile + 1 < g.J) fetch_slots(tile + 1);
+        }
+        wait_or_flush(bar_empty(slot), (use & 1) ^ 1);
+        const char* base = (n & 1) ? vbase : kbase;
+        const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2;
+        if ((tile + 1) * kTN <= g.kv_hi_all) {            // full tile: no zero-fill predicates
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)sl[i] * stride_b, 16u);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const bool ok = sl[i] >= 0;
+            cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)(ok ? sl[i] : 0) * stride_b,
+                        ok ? 16u : 0u);
+          }
+        }
+        rotate(bar_full(slot));
+      }
+    }
+    flush();
+  } else if (warp == 8) {
+    // =================================== MMA issuer =======================================================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
+    constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
+    constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
+    const uint64_t qdesc0 = make_smem_desc(smem + kWsOffQ, 16, 1024);
+    const uint64_t kdesc0 = make_smem_desc(smem + kWsOffRing, 16, 1024);          // K tiles: K-major
+    const uint64_t vdesc0 = make_smem_desc(smem + kWsOffRing, kBlkBytes, 1024);   // V tiles: MN-major
+    auto issue_qk = [&](int t, int f) {                 // f = running ring-fill index of the K tile
+      const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
+      const uint64_t kd = kdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
+#pragma unroll
+      for (int ks = 0; ks < kTD / 16; ++ks) {
+        const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
+        umma_ss_elect(tmem + t * kTN, qd + koff, kd + koff, idesc_qk, ks > 0);
+      }
+      umma_commit_elect(bar_s(t));
+    };
+    auto issue_pv = [&](int t, int f, int half, bool acc) {   // f = running ring-fill index of the V tile
+      const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
+#pragma unroll
+      for (int ks = half * 4; ks < half * 4 + 4; ++ks)
+        umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
+                      (acc || ks > 0));
+    };
+    int fillc = 0, qn = 0;
+    int pc[2] = {0, 0};
+    for (int it = 0;; ++it) {
+      const ItemDesc d = take_item(it);
+      if (!d.valid) break;
+      const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
+      if (g.J == 0) continue;
+      const int base = fillc;
+      mbar_wait(bar_q, qn & 1);
+      mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
+      tc_fence_after();
+      if (g.nt0 > 0) issue_qk(0, base);
+      if (g.nt1 > 0) issue_qk(1, base);
+      umma_commit_elect(bar_empty(base % kRing));                        // K(0) free once both QK(0) are done
+      if (g.J == 1) umma_commit_elect(bar_qfree);                        // last QK of the item: Q may be refilled
+      for (int j = 0; j < g.J; ++j) {
+        const int fv = base + 2 * j + 1, fk = base + 2 * j + 2;
+        mbar_wait(bar_full(fv % kRing), (fv / kRing) & 1);               // V(j)
+        bool k_ready = false;
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          const int ntt = t ? g.nt1 : g.nt0;
+          if (j < ntt) {
+            mbar_wait(bar_p(t, 0), pc[t] & 1);                           // first 64 columns of P_t(j) are in TMEM
+            tc_fence_after();
+            issue_pv(t, fv, 0, j > 0);
+            mbar_wait(bar_p(t, 1), pc[t] & 1);                           // the rest
+            tc_fence_after();
+            issue_pv(t, fv, 1, true);
+            ++pc[t];
+            if (j == ntt - 1) umma_commit_elect(bar_o(t));
+          }
+          if (j + 1 < ntt) {
+            if (!k_ready) {
+              mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);         // K(j+1)
+              tc_fence_after();
+              k_ready = true;
+            }
+            issue_qk(t, fk);
+          }
+        }
+        umma_commit_elect(bar_empty(fv % kRing));
+        if (j + 1 < g.J) umma_commit_elect(bar_empty(fk % kRing));
+        if (j + 2 == g.J) umma_commit_elect(bar_qfree);
+      }
+      fillc += 2 * g.J;
+      ++qn;
+    }
+  } else {
+    // =================================== softmax groups ===================================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 200;\n");
+    const int t = warp >> 2;                          // query tile 0/1
+    const int r = tid & 127;                          // row in the tile == TMEM lane
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem + lane_base + t * kTN;
+    const uint32_t tO = tmem + lane_base + 2 * kTN + t * kTD;
+    int sc = 0, oc = 0;
+    for (int it = 0;; ++it) {
+      const ItemDesc d = take_item(it);
+      if (!d.valid) break;
+      const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
+      const int my_tok = d.j0 + t * tok_per_tile + (r >> log2_g);
+      const int lim = p.causal ? (d.Lkv - d.Lq + my_tok) : (d.Lkv - 1);
+      const int lim0 = p.causal ? (d.Lkv - d.Lq + d.j0 + t * tok_per_tile) : (d.Lkv - 1);
+      const int kv_hi = t ? g.kvhi1 : g.kvhi0;
+      const int ntt = t ? g.nt1 : g.nt0;
+      const int tokst = t ? g.toks1 : g.toks0;
+      float m_used = 0.f, l_run = 0.f;
+      for (int j = 0; j < ntt; ++j, ++sc) {
+        mbar_wait(bar_s(t), sc & 1);
+        tc_fence_after();
+        const int kv0 = j * kTN;
+        const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
+        if (need_mask) {
+          const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
+          softmax_tile<true>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
+        } else {
+          softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
+        }
+      }
+      // ---- epilogue -------------------------------------------------------------------------------------------
+      const bool has = ntt > 0;
+      if (has) {
+        mbar_wait(bar_o(t), oc & 1);
+        ++oc;
+        tc_fence_after();
+      }
+      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+      const bool row_ok = r < (tokst << log2_g);
+      __nv_bfloat16* dst = p.out + (int64_t)(d.q0 + (row_ok ? my_tok : d.j0)) * p.out_row_stride +
+                           (int64_t)(d.kvh * G + (r & (G - 1))) * kTD;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t ov[32];
+        if (has) {
+          tmem_ld_32x32b_x32(tO + c * 32, ov);
+          tmem_wait_ld();
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) ov[e] = 0u;
+        }
+        if (row_ok) {
+#pragma unroll
+          for (int j8 = 0; j8 < 4; ++j8) {
+            uint4 w;
+            w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+            w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+            w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+            w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(dst + c * 32 + j8 * 8) = w;
+          }
+        }
+      }
+      tc_fence_before();   // O_t reads are complete before this group's next P arrive lets PV_t(0) overwrite O_t
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+size_t prefill_sm100_workspace_bytes(int B, int total_q, int group) {
+  int log2_g = 0;
+  while ((1 << log2_g) < group) ++log2_g;
+  const int tok_per_cta = 2 * (kTM >> log2_g);
+  const size_t max_pairs = (size_t)total_q / tok_per_cta + (size_t)B;
+  return kWorkHeaderInts * sizeof(int) + max_pairs * sizeof(int2);
+}
+
+int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   int log2_g = 0;
   while ((1 << log2_g) < p.group) ++log2_g;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSm100Smem);
-    if (e != cudaSuccess) return fail("b200_prefill(sm100): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_set = true;
-  }
-  static const bool stage1 = [] { const char* e = getenv("B200ATTN_PREFILL"); return e && e[0] == 's'; }();
   const int tok_per_tile = kTM >> log2_g;
-  if (stage1) {   // single-tile serial kernel, kept for A/B measurements (B200ATTN_PREFILL=s1)
+  // B200ATTN_PREFILL=s1 / ws select the earlier stages (A/B measurements only)
+  static const char mode = [] { const char* e = getenv("B200ATTN_PREFILL"); return e ? e[0] : 'p'; }();
+  if (mode == 's') {   // stage 1: single-tile serial kernel
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e = cudaFuncSetAttribute(prefill_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSm100Smem);
+      if (e != cudaSuccess) return fail("b200_prefill(sm100): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      attr_set = true;
+    }
     const int max_q_tiles = total_q / tok_per_tile + p.B;   // >= sum_i ceil(Lq_i / tok_per_tile)
     prefill_sm100_kernel<<<dim3(max_q_tiles, p.Hkv), 128, kSm100Smem, st>>>(p, log2_g);
     return check_launch("b200_prefill(sm100 s1)");
   }
-  static bool attr_ws = false;
-  if (!attr_ws) {
-    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
-    if (e != cudaSuccess) return fail("b200_prefill(sm100 ws): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_ws = true;
+  if (mode == 'w') {   // stage 2: warp-specialised, one CTA per 256-row tile
+    static bool attr_ws = false;
+    if (!attr_ws) {
+      cudaError_t e = cudaFuncSetAttribute(prefill_sm100_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
+      if (e != cudaSuccess) return fail("b200_prefill(sm100 ws): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      attr_ws = true;
+    }
+    const int max_ctas = total_q / (2 * tok_per_tile) + p.B;
+    prefill_sm100_ws_kernel<<<dim3(max_ctas, p.Hkv), kWsThreads, kWsSmem, st>>>(p, log2_g);
+    return check_launch("b200_prefill(sm100 ws)");
   }
-  const int max_ctas = total_q / (2 * tok_per_tile) + p.B;
-  prefill_sm100_ws_kernel<<<dim3(max_ctas, p.Hkv), kWsThreads, kWsSmem, st>>>(p, log2_g);
-  return check_launch("b200_prefill(sm100 ws)");
+  // stage 3 (production): device-built work list + persistent kernel, one CTA per SM
+  const size_t need = prefill_sm100_workspace_bytes(p.B, total_q, p.group);
+  if (!workspace || workspace_bytes < need) return fail("b200_prefill: workspace %zu < %zu bytes", workspace_bytes, need);
+  if ((uintptr_t)workspace & 15) return fail("b200_prefill: workspace must be 16-byte aligned");
+  static bool attr_p = false;
+  if (!attr_p) {
+    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
+    if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    attr_p = true;
+  }
+  int* work = reinterpret_cast<int*>(workspace);
+  int2* items = reinterpret_cast<int2*>(work + kWorkHeaderInts);
+  const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
+  prefill_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, 2 * tok_per_tile, work, items, max_pairs);
+  if (int rc = check_launch("b200_prefill(plan)")) return rc;
+  cudaError_t e = launch_pdl(prefill_sm100_persist_kernel, dim3(cached_num_sms()), dim3(kWsThreads), kWsSmem, st, p, log2_g, work,
+                             (const int2*)items);
+  if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): %s", cudaGetErrorString(e));
+  return check_launch("b200_prefill(sm100 persist)");
 }
 
 bool prefill_sm100_supports(int group) { return group >= 1 && group <= 64 && (group & (group - 1)) == 0; }

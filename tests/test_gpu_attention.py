@@ -67,6 +67,10 @@ PREFILL_CASES = [
     ([8, 1, 93, 64], [32, 32, 7, 0], 16, 8, 1), ([300], [0], 32, 8, 1), ([20, 40], [2048, 100], 8, 2, 1),
     ([1, 1, 1], [9, 100, 0], 16, 8, 1), ([200, 31], [16, 48], 16, 8, 16), ([257], [0], 4, 1, 16),
     ([700, 3], [0, 500], 32, 8, 1),
+    # more work items than SMs: every persistent CTA walks several items (heaviest first), ragged tails
+    ([150] * 60, [0] * 60, 16, 8, 1),
+    ([int(x) for x in np.random.default_rng(5).integers(1, 700, 30)], [int(x) for x in np.random.default_rng(6).integers(0, 300, 30)], 32, 8, 1),
+    ([int(x) for x in np.random.default_rng(7).integers(1, 400, 48)], [0] * 48, 4, 1, 16),
 ]
 
 
@@ -78,6 +82,20 @@ def test_prefill_vs_oracle(pkg, q_lens, prefix, Hq, Hkv, ps):
                                 case["kv_indices"], case["last_page_len"], ps, return_fp32=True)
     out = run_prefill(pkg, case)
     check_close(out, ref, f"prefill q{q_lens} p{prefix} Hq{Hq} Hkv{Hkv} ps{ps}")
+
+
+def test_prefill_repeatable_and_workspace_checked(pkg):
+    """The dynamic work list changes the order items are computed in, never their values; a short workspace is
+    an error, not a fallback."""
+    q_lens = [int(x) for x in np.random.default_rng(9).integers(1, 500, 64)]
+    case = make_paged_case(q_lens, 16, 8, q_lens=q_lens, seed=3)
+    a = run_prefill(pkg, case)
+    b = run_prefill(pkg, case)
+    assert torch.equal(a, b)
+    d = dev(case)
+    with pytest.raises(RuntimeError):
+        pkg.ops.prefill(d["q"], d["k_cache"], d["v_cache"], d["qo_indptr"], d["kv_indptr"], d["kv_indices"],
+                        d["last_page_len"], torch.empty(64, dtype=torch.uint8, device="cuda"), 1, 128 ** -0.5, True)
 
 
 def test_prefill_equals_decode_for_single_query(pkg):

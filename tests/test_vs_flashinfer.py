@@ -56,5 +56,6 @@ def test_prefill_matches_flashinfer(pkg):
     except Exception as e:
         pytest.skip(f"flashinfer prefill could not run here: {type(e).__name__}: {e}")
     mine = pkg.ops.prefill(d["q"], d["k_cache"], d["v_cache"], d["qo_indptr"], d["kv_indptr"], d["kv_indices"],
-                           d["last_page_len"], torch.empty(256, dtype=torch.uint8, device="cuda"), 1, 128 ** -0.5, True)
+                           d["last_page_len"], torch.empty(pkg.ops.prefill_workspace_bytes(case["B"], sum(q_lens), Hq, Hkv, 128),
+                                                               dtype=torch.uint8, device="cuda"), 1, 128 ** -0.5, True)
     assert (mine.float() - ref.float()).abs().max().item() <= ATOL
