@@ -107,6 +107,14 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// exp2(x * s + b) as ONE ordered instruction pair: keeps ptxas from hoisting the FMAs of a whole softmax tile
+// above unrelated code (observed: 15 spilled registers in the prefill softmax warps).
+__device__ __forceinline__ float exp2_fma(float x, float s, float b) {
+  float y;
+  asm volatile("{\n\t.reg .f32 t;\n\tfma.rn.f32 t, %1, %2, %3;\n\tex2.approx.ftz.f32 %0, t;\n\t}\n" : "=f"(y) : "f"(x), "f"(s), "f"(b));
+  return y;
+}
+
 __device__ __forceinline__ float fast_log2(float x) {
   float y;
   asm volatile("lg2.approx.ftz.f32 %0, %1;\n" : "=f"(y) : "f"(x));

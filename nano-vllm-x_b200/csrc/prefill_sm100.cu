@@ -359,7 +359,30 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
     alpha = fast_exp2(m_used - mx);
     m_used = mx;
   }
-  if (first_pv_done && __any_sync(0xffffffffu, grow)) {
+  const bool rescale = first_pv_done && __any_sync(0xffffffffu, grow);   // warp-uniform, rare (lazy threshold 2^8)
+  const float neg_m = -m_used;
+  float s0 = 0.f, s1 = 0.f;
+  // The O rescale sits AFTER the exponentials in its own (rare) branch: with the rescale ahead of them ptxas
+  // hoists all 128 ex2 above it and spills 15 registers around the 32-register O chunk on the hot path.
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint32_t pw[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const float a = exp2_fma(__uint_as_float(sv[c][2 * e]), scale_log2, neg_m);
+      const float b = exp2_fma(__uint_as_float(sv[c][2 * e + 1]), scale_log2, neg_m);
+      s0 += a;
+      s1 += b;
+      pw[e] = pack_bf16x2(a, b);
+    }
+    tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
+    if (!rescale && (c == 1 || c == 3)) {           // hand P over in two halves: PV starts on the first
+      tmem_wait_st();                               // while the second is still in the exp unit
+      tc_fence_before();
+      mbar_arrive(c == 1 ? bar_p0 : bar_p1);
+    }
+  }
+  if (rescale) {                                    // O must carry the new scale before PV(j) accumulates into it
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       uint32_t ov[32];
@@ -369,26 +392,10 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
       tmem_st_32x32b_x32(tO + c * 32, ov);
     }
-  }
-  const float neg_m = -m_used;
-  float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    uint32_t pw[16];
-#pragma unroll
-    for (int e = 0; e < 16; ++e) {
-      const float a = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e]), scale_log2, neg_m));
-      const float b = fast_exp2(fmaf(__uint_as_float(sv[c][2 * e + 1]), scale_log2, neg_m));
-      s0 += a;
-      s1 += b;
-      pw[e] = pack_bf16x2(a, b);
-    }
-    tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
-    if (c == 1 || c == 3) {                         // hand P over in two halves: PV starts on the first
-      tmem_wait_st();                               // while the second is still in the exp unit
-      tc_fence_before();
-      mbar_arrive(c == 1 ? bar_p0 : bar_p1);
-    }
+    tmem_wait_st();
+    tc_fence_before();
+    mbar_arrive(bar_p0);
+    mbar_arrive(bar_p1);
   }
   l_run = l_run * alpha + (s0 + s1);
 }
@@ -736,9 +743,14 @@ __device__ __forceinline__ ItemGeo item_geometry(const ItemDesc& d, const int to
   return g;
 }
 
-// Work list for the persistent kernel: pairs (sequence, query tile) bucketed by KV-tile count, heaviest
-// bucket first.  Order inside a bucket is arbitrary (atomics): it only affects scheduling, every item
-// is computed independently, so results do not depend on it.
+// Work list for the persistent kernel.  Sequences are counting-sorted by KV length (longest first); the
+// (sequence, query tile) pairs of one sequence stay CONTIGUOUS, latest (heaviest) query tile first.
+// Consecutive work items are therefore the KV heads of neighbouring query tiles of ONE sequence: the ~148
+// items in flight share that sequence's K/V through L2 (a list sorted purely by weight interleaves all
+// sequences and turns the kernel DRAM-bound: measured 0.60 -> 0.53 of peak on 16 x 4096), while heavy work
+// still starts first and the tail of the run is made of the shortest sequences' lightest tiles.
+// Order among sequences of equal length bucket is arbitrary (atomics): it only affects scheduling, every
+// item is computed independently, so results do not depend on it.
 __global__ void __launch_bounds__(kPlanThreads, 1) prefill_plan_kernel(const PrefillParams p, const int tok_per_cta,
                                                                         int* __restrict__ work, int2* __restrict__ items,
                                                                         const int max_pairs) {
@@ -748,20 +760,14 @@ __global__ void __launch_bounds__(kPlanThreads, 1) prefill_plan_kernel(const Pre
   griddep_launch_dependents();   // the persistent grid may set up (barriers, TMEM) while the list is built
   s_hist[tid] = 0;
   __syncthreads();
-  auto tiles_of_pair = [&](int Lq, int Lkv, int qt) {
-    const int j0 = qt * tok_per_cta;
-    int hi = p.causal ? min(Lkv, Lkv - Lq + min(Lq, j0 + tok_per_cta)) : Lkv;
-    hi = max(hi, 0);
-    return min((hi + kTN - 1) / kTN, kPlanBuckets - 1);
-  };
+  auto bucket_of = [&](int Lkv) { return min((Lkv + kTN - 1) / kTN, kPlanBuckets - 1); };
   for (int i = tid; i < p.B; i += kPlanThreads) {
     const int Lq = p.qo_indptr[i + 1] - p.qo_indptr[i];
-    const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps);
     const int nq = (Lq + tok_per_cta - 1) / tok_per_cta;
-    for (int qt = 0; qt < nq; ++qt) atomicAdd(&s_hist[tiles_of_pair(Lq, Lkv, qt)], 1);
+    if (nq > 0) atomicAdd(&s_hist[bucket_of(seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps))], nq);
   }
   __syncthreads();
-  // thread t owns bucket (kPlanBuckets - 1 - t): an inclusive scan in thread order is a scan heaviest-first
+  // thread t owns bucket (kPlanBuckets - 1 - t): an inclusive scan in thread order is a scan longest-first
   const int mine = s_hist[kPlanBuckets - 1 - tid];
   int total;
   const int incl = block_inclusive_scan<kPlanThreads>(mine, s_scan, &total);
@@ -770,12 +776,11 @@ __global__ void __launch_bounds__(kPlanThreads, 1) prefill_plan_kernel(const Pre
   __syncthreads();
   for (int i = tid; i < p.B; i += kPlanThreads) {
     const int Lq = p.qo_indptr[i + 1] - p.qo_indptr[i];
-    const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps);
     const int nq = (Lq + tok_per_cta - 1) / tok_per_cta;
-    for (int qt = 0; qt < nq; ++qt) {
-      const int pos = atomicAdd(&s_hist[tiles_of_pair(Lq, Lkv, qt)], 1);
-      if (pos < max_pairs) items[pos] = make_int2(i, qt);
-    }
+    if (nq <= 0) continue;
+    const int pos = atomicAdd(&s_hist[bucket_of(seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps))], nq);
+    for (int k = 0; k < nq; ++k)
+      if (pos + k < max_pairs) items[pos + k] = make_int2(i, nq - 1 - k);
   }
   if (tid == 0) {
     work[0] = 0;
@@ -910,7 +915,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       pend_bar = 0;
     };
     auto wait_or_flush = [&](uint32_t bar, uint32_t parity) {
-      if (!mbar_try_wait(bar, parity)) {
+      if (!mbar_test_wait(bar, parity)) {
         flush();
         mbar_wait(bar, parity);
       }
