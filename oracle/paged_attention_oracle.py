@@ -251,6 +251,56 @@ def prefill_attention(q, k_cache, v_cache, qo_indptr, kv_indptr, kv_indices, las
 # --------------------------------------------------------------------------------------
 # synthetic workloads; shared by tests and bench so both sides see the same bytes
 # --------------------------------------------------------------------------------------
+# --------------------------------------------------------------------------------------
+# f-3  q/k RMSNorm + RoPE + slot write (the step just ahead of Attention.forward)
+#      models/qwen3.py:122-134, layers/layernorm.py:16-36, layers/rotary_embedding.py:6-24, 73-102
+# --------------------------------------------------------------------------------------
+def qk_norm_rope_store(qkv: torch.Tensor, positions: torch.Tensor, q_weight: torch.Tensor,
+                       k_weight: torch.Tensor, eps: float, cos_sin_cache: torch.Tensor,
+                       k_cache: torch.Tensor, v_cache: torch.Tensor, slots: torch.Tensor,
+                       Hq: int, Hkv: int, D: int = 128):
+    """Returns (q, k) after per-head RMSNorm + rotary embedding, and scatters (k, v) into the pool.
+
+    Restates, per token and head (fp32 arithmetic, ONE rounding to the activation dtype per module
+    output, which is what the reference's ``@torch.compile``d modules produce on the GPU; run
+    eagerly the RoPE products round to bf16 three times, <= 2 bf16 ulp away -- the golden test
+    bounds that difference):
+      * ``qkv.split([q_size, kv_size, kv_size])`` and the per-head views (models/qwen3.py:123-132);
+      * RMSNorm without residual (layers/layernorm.py:24-33): ``x.float()``,
+        ``x * rsqrt(mean(x^2) + eps)``, ``(x * weight).to(dtype)``;
+      * RotaryEmbedding.forward (layers/rotary_embedding.py:87-101) with ``rotary_dim == head_size``:
+        ``cos, sin = cos_sin_cache[pos].chunk(2)``, cast to the activation dtype (:16-17),
+        ``x1, x2 = chunk(x, 2)``, ``o1 = x1*cos - x2*sin``, ``o2 = x2*cos + x1*sin`` and the
+        INTERLEAVED output ``stack((o1, o2), -1).flatten(-2)`` (:19-24);
+      * the slot write of Attention.forward (layers/attention.py:347-352): see store_kvcache.
+    """
+    T = qkv.shape[0]
+    dt = qkv.dtype
+    q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+
+    def norm(x, w):
+        xf = x.reshape(T, -1, D).float()
+        var = xf.pow(2).mean(dim=-1, keepdim=True)
+        xf = xf * torch.rsqrt(var + eps)
+        return (xf * w.float()).to(dt)
+
+    cs = cos_sin_cache.index_select(0, positions.reshape(-1).long())
+    cos, sin = cs.chunk(2, dim=-1)
+    cos = cos.unsqueeze(-2).to(dt).float()
+    sin = sin.unsqueeze(-2).to(dt).float()
+
+    def rope(x):
+        x1, x2 = torch.chunk(x.float(), 2, dim=-1)
+        o1 = x1 * cos - x2 * sin
+        o2 = x2 * cos + x1 * sin
+        return torch.stack((o1, o2), dim=-1).flatten(-2).to(dt)
+
+    qo = rope(norm(q, q_weight))
+    ko = rope(norm(k, k_weight))
+    store_kvcache(ko, v.reshape(T, Hkv, D), k_cache, v_cache, slots)
+    return qo.reshape(T, Hq * D), ko.reshape(T, Hkv * D)
+
+
 def bench_workload(num_seqs: int = 256, max_input_len: int = 1024, max_output_len: int = 1024,
                    seed_value: int = 0):
     """Request generator of the reference's bench.py:14-29 (python ``random`` with seed 0:
