@@ -199,15 +199,21 @@ class Layer(torch.nn.Module):
         self.attn = AttnCls(self.Hq, D, None, self.Hkv, layer_id)
         self.tp = tp
 
-    def forward(self, x, cos, sin):
+    def forward(self, x, cos, sin, pos=None, cos_sin_cache=None):
         T = x.shape[0]
         h = F.rms_norm(x, (x.shape[-1],), self.ln1, 1e-6)
         qkv = h @ self.qkv.t()
+        if cos_sin_cache is not None:      # q/k norm + RoPE + slot write in one kernel ahead of attention
+            o = self.attn.forward_fused_qkv(qkv, pos, self.qn, self.kn, 1e-6, cos_sin_cache)
+            return self._tail(x, o)
         q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
         q = F.rms_norm(q.reshape(T, self.Hq, self.D), (self.D,), self.qn, 1e-6)
         k = F.rms_norm(k.reshape(T, self.Hkv, self.D), (self.D,), self.kn, 1e-6)
         q, k = rope(q, cos, sin), rope(k, cos, sin)
         o = self.attn(q.reshape(T, -1), k.reshape(T, -1), v)        # v stays a strided view of qkv (qwen3.py:123)
+        return self._tail(x, o)
+
+    def _tail(self, x, o):
         o = o @ self.o.t()
         if self.tp > 1:
             dist.all_reduce(o)
@@ -239,9 +245,15 @@ class Model(torch.nn.Module):
         t = torch.arange(ctx, device=dev, dtype=torch.float32)
         fr = torch.outer(t, inv)
         self.cos, self.sin = fr.cos(), fr.sin()
+        self.cos_sin_cache = torch.cat((self.cos, self.sin), dim=-1).contiguous()   # rotary_embedding.py:62-71 layout
+        self.fused = False
 
     def forward(self, ids, pos):
         x = self.embed[ids]
+        if self.fused:
+            for l in self.layers:
+                x = l(x, None, None, pos, self.cos_sin_cache)
+            return F.rms_norm(x, (x.shape[-1],), self.norm, 1e-6)
         cos, sin = self.cos[pos][:, None, :], self.sin[pos][:, None, :]
         for l in self.layers:
             x = l(x, cos, sin)
@@ -260,6 +272,8 @@ def main():
     ap.add_argument("--max-steps", type=int, default=0, help="stop after this many engine steps (0 = run to completion)")
     ap.add_argument("--dump-tokens", default=None)
     ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--fused-qk", action="store_true",
+                    help="b200 backend only: q/k RMSNorm + RoPE + slot write as one kernel (SURVEY.md f-3)")
     a = ap.parse_args()
 
     import nanovllmx_b200 as pkg
@@ -285,6 +299,7 @@ def main():
     torch.manual_seed(0)
     with torch.inference_mode():
         model = Model(cfg, tp, AttnCls, dev, a.context_len)
+        model.fused = bool(a.fused_qk and a.backend == "b200")
         pool = PoolCls(torch.bfloat16, dev, num_slots, cfg["L"], Hkv, D)
         backend = BackendCls(pool, Hq, Hkv, D, torch.bfloat16, dev)
         free = list(range(num_slots - 1, -1, -1))            # LIFO, fresh pool hands out 0,1,2,... (kv_cache.py:108-114)
@@ -416,7 +431,7 @@ def main():
         res = dict(model=a.model, backend=a.backend, tp=tp, num_seqs=a.num_seqs, wall_s=wall, steps=steps, prefill_steps=n_prefill,
                    decode_steps=n_decode, prefill_s=t_prefill, decode_s=t_decode, generated_tokens=generated,
                    sum_max_tokens=sum(max_tokens), tok_s_reference_formula=sum(max_tokens) / wall,
-                   tok_s_generated=generated / wall, graph_capture_s=t_cap, greedy=a.greedy,
+                   tok_s_generated=generated / wall, graph_capture_s=t_cap, greedy=a.greedy, fused_qk=model.fused,
                    prompt_tokens=sum(len(p) for p in prompts))
         print(json.dumps(res), flush=True)
         if a.dump_tokens:

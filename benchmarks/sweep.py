@@ -4,7 +4,7 @@
 kernel semantics via torch index_copy as a stand-in is NOT used: FlashInfer/Triton only).
 BASELINE.md M1-M3.  CUDA-event timing, inputs >> L2 or L2 flushed between iterations.
 
-  python benchmarks/sweep.py [decode|prefill|store|meta|all] [--no-flashinfer]
+  python benchmarks/sweep.py [decode|prefill|store|qknorm|meta|all] [--no-flashinfer]
 """
 import argparse
 import json
@@ -240,6 +240,58 @@ def bench_store():
     return rows
 
 
+def bench_qknorm():
+    """f-3: the fused q/k RMSNorm + RoPE + slot write kernel vs the unfused sequence of the reference
+    (models/qwen3.py:123-134: q_norm, k_norm, rotary_emb as separate elementwise kernels, then the slot write),
+    restated with stock torch ops (F.rms_norm + eager RoPE) + this repo's store kernel."""
+    import torch.nn.functional as F
+    rows = []
+    D, max_pos = 128, 4096
+    inv = 1.0 / (1e6 ** (torch.arange(0, D, 2, dtype=torch.float, device=DEV) / D))
+    fr = torch.outer(torch.arange(max_pos, dtype=torch.float, device=DEV), inv)
+    cache = torch.cat((fr.cos(), fr.sin()), -1).contiguous()
+    for T, Hq, Hkv in [(256, 16, 8), (256, 32, 8), (256, 4, 1), (16384, 32, 8), (142827, 16, 8), (142827, 32, 8), (142827, 4, 1)]:
+        qkv = torch.randn((T, (Hq + 2 * Hkv) * D), device=DEV, dtype=torch.bfloat16)
+        qw = torch.ones(D, device=DEV, dtype=torch.bfloat16)
+        kw = torch.ones(D, device=DEV, dtype=torch.bfloat16)
+        pos = torch.randint(0, max_pos, (T,), device=DEV)
+        pool = max(2 * T, 4096)
+        kc = torch.empty((pool, Hkv, D), device=DEV, dtype=torch.bfloat16)
+        vc = torch.empty_like(kc)
+        slots = torch.randperm(pool, device=DEV)[:T]
+        q_view = qkv[:, : Hq * D]
+        f = lambda: pkg.ops.qk_norm_rope_store(qkv, pos, qw, kw, 1e-6, cache, q_view, None, kc, vc, slots, Hq, Hkv, D)
+        ms = timeit(f, flush=True)
+        by = 2 * T * (Hq + 2 * Hkv) * D * 2 + 16 * T
+        row = dict(case="qk_norm_rope_store", T=T, Hq=Hq, Hkv=Hkv, MB=by / 1e6, ms=ms, GBs=by / ms / 1e6,
+                   frac_measured=by / ms / 1e6 / PEAK)
+        if T <= 1024:
+            row["graph_ms"] = time_graph(f)
+
+        def unfused():
+            q, k, v = qkv.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+            qh = F.rms_norm(q.reshape(T, Hq, D), (D,), qw, 1e-6)
+            kh = F.rms_norm(k.reshape(T, Hkv, D), (D,), kw, 1e-6)
+            cs = cache.index_select(0, pos)
+            cos, sin = cs[:, None, : D // 2].to(qh.dtype), cs[:, None, D // 2:].to(qh.dtype)
+
+            def rope(x):
+                x1, x2 = x.chunk(2, -1)
+                return torch.stack((x1 * cos - x2 * sin, x2 * cos + x1 * sin), -1).flatten(-2)
+            qo, ko = rope(qh), rope(kh)
+            pkg.store_kvcache(ko, v.view(T, Hkv, D), kc, vc, slots)
+            return qo
+        try:
+            row["unfused_torch_eager_ms"] = timeit(unfused, flush=True)
+            if T <= 1024:
+                row["unfused_graph_ms"] = time_graph(unfused)
+        except Exception as e:
+            row["unfused"] = str(e)[:80]
+        print(json.dumps(row), flush=True)
+        rows.append(row)
+    return rows
+
+
 def bench_meta():
     """Host wall time per step of the metadata build at bench-like decode shape (B=256, L~1-2k):
     ours (one message + 3 kernels) vs the reference's algorithm (2B H2D copies + B .item() syncs),
@@ -304,6 +356,8 @@ if __name__ == "__main__":
         res["prefill"] = bench_prefill(not a.no_flashinfer)
     if a.what in ("store", "all"):
         res["store"] = bench_store()
+    if a.what in ("qknorm", "all"):
+        res["qknorm"] = bench_qknorm()
     if a.what in ("meta", "all"):
         res["meta"] = bench_meta()
     if a.out:

@@ -149,6 +149,36 @@ int b200_prefill(const void* q, int64_t q_row_stride, const void* k_cache, const
                  int32_t total_q, int32_t Hq, int32_t Hkv, int32_t D, int32_t page_size,
                  float sm_scale, int32_t causal, int32_t dtype, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * (f-3) Fused q/k RMSNorm + rotary embedding + KV slot write: the step just ahead of
+ *     Attention.forward in Qwen3Attention.forward (models/qwen3.py:122-134).  One launch replaces
+ *     q_norm / k_norm (layers/layernorm.py:16-36), rotary_emb (layers/rotary_embedding.py:73-102)
+ *     and the slot write of Attention.forward (layers/attention.py:347-352 -> core/kv_cache.py:12-44);
+ *     the caller then runs Attention.forward(q, None, None) (attention only).
+ *
+ *     qkv         : [T, (Hq + 2 Hkv) * D] output of qkv_proj, rows qkv_row_stride elements apart,
+ *                   laid out [q heads | k heads | v heads] (models/qwen3.py:123)
+ *     positions   : int64 [T] (core/model_runner.py:175-189)
+ *     q_weight,   : [D] RMSNorm weights of q_norm / k_norm, activation dtype
+ *     k_weight
+ *     cos_sin_cache : fp32 [max_pos, D] = [cos(D/2) | sin(D/2)] per position, rows
+ *                   cos_sin_row_stride elements apart (RotaryEmbedding.cos_sin_cache,
+ *                   layers/rotary_embedding.py:62-71; rotary_dim == head_dim)
+ *     q_out       : [T, Hq * D]; may alias the q part of qkv (in place)
+ *     k_out       : [T, Hkv * D] or NULL (the normalised+rotated K is otherwise only written to the pool)
+ *     k_cache,    : [num_slots, Hkv, D] layer views of the pool; slots int64 [T], slot < 0 =>
+ *     v_cache       that token's K/V are not written (CUDA-graph padding, layers/attention.py:265)
+ *     Output layout of the rotary step is the reference's INTERLEAVED one (out[2i] = o1[i],
+ *     out[2i+1] = o2[i], layers/rotary_embedding.py:24), so pools stay interchangeable.
+ *     Only D == 128 and bf16 are built.
+ * ---------------------------------------------------------------------------------------- */
+int b200_qk_norm_rope_store(const void* qkv, int64_t qkv_row_stride, const int64_t* positions,
+                            const void* q_weight, const void* k_weight, float eps,
+                            const float* cos_sin_cache, int64_t cos_sin_row_stride, int32_t max_pos,
+                            void* q_out, int64_t q_out_row_stride, void* k_out, int64_t k_out_row_stride,
+                            void* k_cache, void* v_cache, const int64_t* slots, int32_t T, int32_t Hq,
+                            int32_t Hkv, int32_t D, int32_t dtype, b200_stream_t stream);
+
 /* Counters for bench.py's `gpu_launches`: number of kernels this library has launched in this
  * process since load / since the last reset. */
 int64_t b200_launch_count(void);

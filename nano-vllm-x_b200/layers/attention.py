@@ -353,17 +353,34 @@ class Attention(nn.Module):
     def set_attention_metadata(self, metadata: Optional[AttentionMetadata]) -> None:
         self.attention_metadata = metadata
 
+    def forward_fused_qkv(self, qkv: torch.Tensor, positions: torch.Tensor, q_norm_weight: torch.Tensor,
+                          k_norm_weight: torch.Tensor, eps: float, cos_sin_cache: torch.Tensor) -> torch.Tensor:
+        """what Qwen3Attention.forward does between qkv_proj and o_proj (models/qwen3.py:123-134:
+        split, q_norm, k_norm, rotary_emb, then Attention.forward with its slot write, reference :347-352) with ONE
+        kernel ahead of the attention kernel.  q is normalised/rotated in place inside ``qkv``; K (normalised,
+        rotated, the reference's interleaved layout) and V go straight to the pool rows ``output_kv_indices``."""
+        md = self.attention_metadata
+        assert md is not None
+        Hq, Hkv, D = self.num_heads, self.num_kv_heads, self.head_dim
+        qkv = qkv.view(-1, (Hq + 2 * Hkv) * D)
+        k_cache, v_cache = md.kv_cache.get_kv_cache(self.layer_id)
+        q = qkv[:, : Hq * D]
+        ops.qk_norm_rope_store(qkv, positions.reshape(-1), q_norm_weight, k_norm_weight, eps, cos_sin_cache, q, None,
+                               k_cache, v_cache, md.output_kv_indices, Hq, Hkv, D)
+        return self.forward(q, None, None)
+
     def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, save_kv_cache: bool = True):
         md = self.attention_metadata
         assert md is not None
-        q = q.contiguous()
+        if q.dim() != 2 or q.stride(-1) != 1 or q.stride(0) % 8 or q.data_ptr() % 16:
+            q = q.contiguous()      # the kernels take a row stride: a column slice of the qkv buffer is read in place
         if k is not None:
             assert v is not None
             if save_kv_cache:
                 md.kv_cache.set_kv_cache(self.layer_id, md.output_kv_indices,
                                          k.view(-1, self.num_kv_heads, self.head_dim),
                                          v.view(-1, self.num_kv_heads, self.head_dim))
-        q = q.view(-1, self.num_heads, self.head_dim)
+        q = q.unflatten(-1, (self.num_heads, self.head_dim))
         k_cache, v_cache = md.kv_cache.get_kv_cache(self.layer_id)
         name = mode_name(md.forward_mode)
         if name not in ("PREFILL", "DECODE"):

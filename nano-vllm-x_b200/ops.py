@@ -178,6 +178,38 @@ def _(q, k_cache, v_cache, qo_indptr, kv_indptr, kv_indices, last_page_len, work
     return torch.empty_like(q)
 
 
+# ---- (f-3) fused q/k RMSNorm + RoPE + slot write ------------------------------------------------------
+@torch.library.custom_op("b200attn::qk_norm_rope_store", mutates_args=("q_out", "k_out", "k_cache", "v_cache"),
+                         device_types="cuda")
+def qk_norm_rope_store(qkv: torch.Tensor, positions: torch.Tensor, q_weight: torch.Tensor, k_weight: torch.Tensor,
+                       eps: float, cos_sin_cache: torch.Tensor, q_out: torch.Tensor, k_out: torch.Tensor | None,
+                       k_cache: torch.Tensor, v_cache: torch.Tensor, slots: torch.Tensor, Hq: int, Hkv: int,
+                       D: int) -> None:
+    """models/qwen3.py:123-133 + layers/attention.py:347-352 in one launch (see include/b200attn.h, f-3).
+    ``q_out`` may be the q columns of ``qkv`` itself (in place)."""
+    _need_cuda(qkv, positions, q_weight, k_weight, cos_sin_cache, q_out, k_cache, v_cache, slots)
+    T = qkv.shape[0]
+    assert qkv.dim() == 2 and qkv.shape[1] == (Hq + 2 * Hkv) * D and qkv.stride(1) == 1
+    assert qkv.dtype in _DTYPE_CODE and q_out.dtype == qkv.dtype == k_cache.dtype == v_cache.dtype
+    assert q_weight.dtype == qkv.dtype and k_weight.dtype == qkv.dtype and q_weight.numel() == D and k_weight.numel() == D
+    assert q_weight.is_contiguous() and k_weight.is_contiguous()
+    assert positions.dtype == torch.int64 and positions.numel() == T and positions.is_contiguous()
+    assert slots.dtype == torch.int64 and slots.numel() == T and slots.is_contiguous()
+    assert cos_sin_cache.dtype == torch.float32 and cos_sin_cache.dim() == 2 and cos_sin_cache.shape[1] == D \
+        and cos_sin_cache.stride(1) == 1, "RotaryEmbedding.cos_sin_cache must be fp32 [max_pos, head_dim]"
+    assert q_out.dim() == 2 and q_out.shape == (T, Hq * D) and q_out.stride(1) == 1
+    assert k_out is None or (k_out.shape == (T, Hkv * D) and k_out.stride(1) == 1 and k_out.dtype == qkv.dtype)
+    row = Hkv * D
+    assert k_cache.stride(-3) == row and v_cache.stride(-3) == row and k_cache.stride(-1) == 1 and k_cache.stride(-2) == D
+    lib = _lib.load()
+    rc = lib.b200_qk_norm_rope_store(qkv.data_ptr(), qkv.stride(0), positions.data_ptr(), q_weight.data_ptr(),
+                                     k_weight.data_ptr(), float(eps), cos_sin_cache.data_ptr(), cos_sin_cache.stride(0),
+                                     cos_sin_cache.shape[0], q_out.data_ptr(), q_out.stride(0), _ptr(k_out),
+                                     0 if k_out is None else k_out.stride(0), k_cache.data_ptr(), v_cache.data_ptr(),
+                                     slots.data_ptr(), T, Hq, Hkv, D, _DTYPE_CODE[qkv.dtype], _stream())
+    _lib.check(rc, "b200_qk_norm_rope_store")
+
+
 def launch_count() -> int:
     return int(_lib.load().b200_launch_count())
 

@@ -29,6 +29,9 @@ def test_loader_and_error_path(pkg):
     assert rc != 0 and b"null" in lib.b200_last_error()
     rc = lib.b200_build_meta(None, 0, None, 1, 1, 3, 0, None, None, None, 0, None, None, 0, None, None)
     assert rc != 0 and b"power of two" in lib.b200_last_error()
+    rc = lib.b200_qk_norm_rope_store(None, 0, None, None, None, 1e-6, None, 0, 0, None, 0, None, 0, None, None, None, 4, 16, 8, 64,
+                                     0, None)
+    assert rc != 0 and b"head_dim 128" in lib.b200_last_error()
     rc = lib.b200_decode(None, 0, None, None, 0, None, None, None, None, 0, None, 0, 1, 8, 8, 64, 1, 1.0, 0, None)
     assert rc != 0 and b"head_dim" in lib.b200_last_error()
 
@@ -36,7 +39,7 @@ def test_loader_and_error_path(pkg):
 def test_ops_registered_and_no_cpu_fallback(pkg):
     import pytest
     import torch
-    for name in ("store_kv", "slot_table_update", "build_meta", "step_meta", "decode", "prefill"):
+    for name in ("store_kv", "slot_table_update", "build_meta", "step_meta", "decode", "prefill", "qk_norm_rope_store"):
         assert hasattr(torch.ops.b200attn, name)
     k = torch.zeros(2, 1, 8, dtype=torch.bfloat16)
     with pytest.raises(Exception):
