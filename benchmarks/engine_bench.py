@@ -272,6 +272,14 @@ def main():
     ap.add_argument("--max-steps", type=int, default=0, help="stop after this many engine steps (0 = run to completion)")
     ap.add_argument("--dump-tokens", default=None)
     ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--kernel-profile", default=None,
+                    help="write a per-kernel GPU time table (torch.profiler / CUPTI) of decode steps 100..120 to this file")
+    ap.add_argument("--workload", default="bench", choices=["bench", "shared-prefix"],
+                    help="bench = reference bench.py:14-29; shared-prefix = BASELINE.json configs[3] (SURVEY.md 8d config 4): "
+                         "256 requests = one 2048-token system prompt (seed 1) + suffix randint(16,256), 128 new tokens")
+    ap.add_argument("--prefix-cache", action="store_true",
+                    help="SURVEY.md f-1: admission-time prefix reuse (longest cached prefix of token_ids[:-1] seeds "
+                         "kv_indices / cached_kv_len, as RadixTree.match_prefix would at core/scheduler.py:67-74)")
     ap.add_argument("--fused-qk", action="store_true",
                     help="b200 backend only: q/k RMSNorm + RoPE + slot write as one kernel (SURVEY.md f-3)")
     a = ap.parse_args()
@@ -293,9 +301,17 @@ def main():
     else:
         PoolCls, BackendCls, AttnCls = make_flashinfer_backend(pkg)
 
-    prompts, max_tokens = bench_workload(a.num_seqs)
+    system_prompt = None
+    if a.workload == "bench":
+        prompts, max_tokens = bench_workload(a.num_seqs)
+    else:
+        import random
+        rng = random.Random(1)
+        system_prompt = [rng.randint(0, 10000) for _ in range(2048)]
+        prompts = [system_prompt + [rng.randint(0, 10000) for _ in range(rng.randint(16, 256))] for _ in range(a.num_seqs)]
+        max_tokens = [len(p) + 128 for p in prompts]             # max_tokens caps prompt + generated (core/engine.py:149)
     prompts = [[t % cfg["vocab"] for t in p] for p in prompts]
-    num_slots = sum(max(len(p), m) + 1 for p, m in zip(prompts, max_tokens)) + 1024
+    num_slots = sum(max(len(p), m) + 1 for p, m in zip(prompts, max_tokens)) + 1024 + 4096
     torch.manual_seed(0)
     with torch.inference_mode():
         model = Model(cfg, tp, AttnCls, dev, a.context_len)
@@ -349,14 +365,24 @@ def main():
                 last.append(c - 1)
             return h[last]
 
+        prof = dict(ids=0.0, meta=0.0, replay=0.0, sample=0.0, book=0.0, gpu_graph_ms=0.0, n=0)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
         def run_graph(batch):
             bs = batch.num_seqs
             padded = graph.match_bs(bs)
+            t0 = time.perf_counter()
             ids_buf[:bs] = torch.tensor([s.token_ids[-1] for s in batch.seqs], dtype=torch.long, device=dev)
             pos_buf[:bs] = torch.tensor([len(s.token_ids) - 1 for s in batch.seqs], dtype=torch.long, device=dev)
+            t1 = time.perf_counter()
             md = backend.build_metadata_for_cuda_graph_replay(graph, batch, padded)
+            t2 = time.perf_counter()
             with pkg.attention_kv_cache(model, md) if a.backend == "b200" else _ctx(model, md):
+                ev[0].record()
                 graph.replay(padded)
+                ev[1].record()
+            t3 = time.perf_counter()
+            prof["ids"] += t1 - t0; prof["meta"] += t2 - t1; prof["replay"] += t3 - t2; prof["n"] += 1
             return hid_buf[:bs]
 
         # warm-up outside the timed region (the reference's bench.py:31 does one warm-up generate): JIT compiles
@@ -374,23 +400,79 @@ def main():
             free.extend(reversed(s.kv_indices))
         free.sort(reverse=True)
         margins.clear()
+        # ---- f-1: minimal prefix cache (what KVCacheManager.cache_sequence + RadixTree.match_prefix provide) ----------
+        cached = []                                   # [(token_ids, kv_indices)] of finished sequences; slots stay allocated
+        shared_slots = set()
+
+        def match_prefix(tokens):
+            best_n, best = 0, None
+            for ct, ck in cached:
+                n, lim = 0, min(len(ct), len(tokens))
+                while n < lim and ct[n] == tokens[n]:
+                    n += 1
+                if n > best_n:
+                    best_n, best = n, ck
+            return best_n, best
+
+        def admit(s):
+            if a.prefix_cache:
+                n, ck = match_prefix(s.token_ids[:-1])             # always leave >= 1 token to compute
+                if n:
+                    s.kv_indices = list(ck[:n])
+                    s.cached_kv_len = n
+            s.kv_indices.extend(free.pop() for _ in range(len(s.token_ids) - len(s.kv_indices)))
+
+        def release(s):
+            free.extend(x for x in s.kv_indices if x not in shared_slots)
+
+        prefix_warm_s = 0.0
+        if system_prompt is not None and a.prefix_cache:
+            # a finished earlier request has left the system prompt in the cache (the reference caches at finish only,
+            # core/scheduler.py:189 -> core/kv_cache.py:333-369); done outside the timed region and reported
+            tw = time.perf_counter()
+            w = Seq("sys", [t % cfg["vocab"] for t in system_prompt] + [1], len(system_prompt) + 2)
+            admit(w)
+            sample(run_eager(Batch(pkg.ForwardMode.PREFILL, [w])))
+            torch.cuda.synchronize()
+            cached.append((list(w.token_ids), list(w.kv_indices)))
+            shared_slots.update(w.kv_indices)
+            prefix_warm_s = time.perf_counter() - tw
+        margins.clear()
         waiting = [Seq(f"r{i}", p, m) for i, (p, m) in enumerate(zip(prompts, max_tokens))]
         running, done = [], []
-        steps = n_prefill = n_decode = generated = 0
+        steps = n_prefill = n_decode = generated = prefill_tokens = 0
         t_prefill = t_decode = 0.0
         out_tokens = {}
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
+        kprof = None
         while waiting or running:
+            if a.kernel_profile and rank == 0:
+                if n_decode == 100 and kprof is None:
+                    torch.cuda.synchronize()
+                    kprof = torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA])
+                    kprof.__enter__()
+                elif n_decode == 120 and kprof is not None and kprof != "done":
+                    torch.cuda.synchronize()
+                    kprof.__exit__(None, None, None)
+                    rows = [(e.key, e.device_time_total, e.count) for e in kprof.key_averages()]
+                    rows.sort(key=lambda r: -r[1])
+                    tot = sum(r[1] for r in rows)
+                    with open(a.kernel_profile, "w") as f:
+                        f.write(f"# decode steps 100..119, batch {len(running)}, total GPU kernel time {tot / 20:.1f} us/step\n")
+                        for k, us, n in rows:
+                            f.write(f"{us / 20:10.2f} us/step  {100 * us / tot:5.1f}%  x{n / 20:6.1f}/step  {k[:150]}\n")
+                    kprof = "done"
             ts = time.perf_counter()
             take = waiting[: a.max_bs - len(running)] if waiting else []
             if take:
                 waiting = waiting[len(take):]
                 for s in take:
-                    s.kv_indices.extend(free.pop() for _ in range(len(s.token_ids)))
+                    admit(s)
                 batch = Batch(pkg.ForwardMode.PREFILL, take)
+                prefill_tokens += sum(len(s.token_ids) - s.cached_kv_len for s in take)
                 toks = sample(run_eager(batch))
                 n_prefill += 1
                 mode = "p"
@@ -398,12 +480,18 @@ def main():
                 for s in running:
                     s.kv_indices.append(free.pop())
                 batch = Batch(pkg.ForwardMode.DECODE, running)
-                toks = sample(run_eager(batch) if a.eager else run_graph(batch))
+                hid = run_eager(batch) if a.eager else run_graph(batch)
+                tsm = time.perf_counter()
+                toks = sample(hid)
                 n_decode += 1
                 mode = "d"
             if world > 1:
                 dist.broadcast(toks, 0)          # all ranks must append identical tokens
             toks = toks.tolist()
+            if mode == "d" and not a.eager:
+                tb = time.perf_counter()
+                prof["sample"] += tb - tsm
+                prof["gpu_graph_ms"] += ev[0].elapsed_time(ev[1])
             keep = []
             mg = margins[-1].tolist() if a.greedy else None
             for si, (s, t) in enumerate(zip(batch.seqs, toks)):
@@ -412,7 +500,7 @@ def main():
                 out_tokens.setdefault(s.seq_id, []).append(t if mg is None else (t, round(mg[si], 5)))
                 generated += 1
                 if len(s.token_ids) >= s.max_tokens:                 # core/engine.py:149
-                    free.extend(s.kv_indices)
+                    release(s)
                     done.append(s)
                 else:
                     keep.append(s)
@@ -422,6 +510,8 @@ def main():
             else:
                 running = keep
                 t_decode += time.perf_counter() - ts
+                if not a.eager:
+                    prof["book"] += time.perf_counter() - tb
             steps += 1
             if a.max_steps and steps >= a.max_steps:
                 break
@@ -431,8 +521,14 @@ def main():
         res = dict(model=a.model, backend=a.backend, tp=tp, num_seqs=a.num_seqs, wall_s=wall, steps=steps, prefill_steps=n_prefill,
                    decode_steps=n_decode, prefill_s=t_prefill, decode_s=t_decode, generated_tokens=generated,
                    sum_max_tokens=sum(max_tokens), tok_s_reference_formula=sum(max_tokens) / wall,
-                   tok_s_generated=generated / wall, graph_capture_s=t_cap, greedy=a.greedy, fused_qk=model.fused,
+                   tok_s_generated=generated / wall, graph_capture_s=t_cap, workload=a.workload, prefix_cache=a.prefix_cache,
+                   prefill_tokens_computed=prefill_tokens, prefix_warm_s=prefix_warm_s, greedy=a.greedy, fused_qk=model.fused,
                    prompt_tokens=sum(len(p) for p in prompts))
+        if prof["n"]:
+            # per decode step, host wall ms: building ids/positions, attention metadata (the hot path's host side), graph
+            # launch, sampling incl. waiting for the GPU, python bookkeeping; and the GPU time of the captured graph
+            res["decode_step_ms"] = {k: round(1e3 * v / prof["n"], 4) if k != "gpu_graph_ms" else round(v / prof["n"], 4)
+                                     for k, v in prof.items() if k != "n"}
         print(json.dumps(res), flush=True)
         if a.dump_tokens:
             json.dump(out_tokens, open(a.dump_tokens, "w"))
