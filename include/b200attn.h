@@ -31,6 +31,7 @@ typedef void* b200_stream_t; /* cudaStream_t */
 /* dtype codes for K/V/Q/O element type */
 #define B200_DTYPE_BF16 0
 #define B200_DTYPE_FP16 1
+#define B200_DTYPE_FP32 2 /* b200_sample logits only */
 
 int b200_abi_version(void);
 const char* b200_last_error(void);
@@ -178,6 +179,33 @@ int b200_qk_norm_rope_store(const void* qkv, int64_t qkv_row_stride, const int64
                             void* q_out, int64_t q_out_row_stride, void* k_out, int64_t k_out_row_stride,
                             void* k_cache, void* v_cache, const int64_t* slots, int32_t T, int32_t Hq,
                             int32_t Hkv, int32_t D, int32_t dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (f-4) Sampler tail.  Replaces Sampler.forward (layers/sampler.py:19-55) with its helpers
+ *     _apply_top_k_top_p (:58-90, a full-vocabulary sort) and _apply_min_p (:93-106), called from
+ *     ModelRunner.execute_model (core/model_runner.py:262-272) with the tensors of
+ *     prepare_sampling_params (:191-219).  One launch, no sort, no [B, V] temporaries.
+ *
+ *     logits      : [B, V] bf16 (what compute_logits returns) or fp32, rows row_stride elements apart
+ *     temperatures: fp32 [B] or NULL          top_ks : int64 [B] or NULL (>= V = off; the reference
+ *     top_ps      : fp32 [B] or NULL                   sends vocab_size for top_k == -1, :203-206)
+ *     min_ps      : fp32 [B] or NULL
+ *                   all four NULL => greedy argmax (layers/sampler.py:28-36); a row whose temperature
+ *                   is <= 0 is greedy too (the reference would divide by zero)
+ *     noise       : fp32 [B, V] Exp(1) samples, rows noise_row_stride apart, or NULL.  torch.multinomial
+ *                   (layers/sampler.py:53) is argmax(probs / q) with q = empty_like(probs).exponential_(1);
+ *                   passing that q reproduces the reference's draw.  NULL => q comes from
+ *                   Philox-4x32-10(counter = (column / 4, row, offset), key = seed), word column % 4,
+ *                   u = ((word >> 8) + 0.5) * 2^-24, q = -log u.
+ *     out_ids     : int64 [B]
+ *     Order of operations as the reference: logits / T, top-k (ties at the k-th value kept), top-p
+ *     over the top-k survivors in ascending (value, index) order with the last one always kept,
+ *     min-p, then the draw.  V <= 2^24.
+ * ---------------------------------------------------------------------------------------- */
+int b200_sample(const void* logits, int64_t row_stride, int32_t logits_dtype, int32_t B, int32_t V,
+                const float* temperatures, const int64_t* top_ks, const float* top_ps,
+                const float* min_ps, const float* noise, int64_t noise_row_stride, uint64_t seed,
+                uint64_t offset, int64_t* out_ids, b200_stream_t stream);
 
 /* Counters for bench.py's `gpu_launches`: number of kernels this library has launched in this
  * process since load / since the last reset. */

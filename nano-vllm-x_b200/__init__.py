@@ -7,6 +7,7 @@ with ``importlib.import_module("nano-vllm-x_b200")`` or through the one-line ali
   layers/attention.py  <- nanovllmx/layers/attention.py   (Attention, AttentionBackend, ...)
   core/kv_cache.py     <- nanovllmx/core/kv_cache.py:12-99 (KVCachePool, store_kvcache)
   core/cuda_graph.py   <- nanovllmx/core/cuda_graph.py     (graph registry used by the API)
+  layers/sampler.py    <- nanovllmx/layers/sampler.py      (Sampler)
   ops.py / _lib.py        torch.library ops over the C ABI of include/b200attn.h
   csrc/                   CUDA kernels for sm_100a + the extern "C" entry points
 """
@@ -17,6 +18,7 @@ from .core.cuda_graph import CUDAGraph                             # noqa: F401
 from .core.kv_cache import KVCachePool, store_kvcache              # noqa: F401
 from .layers.attention import (Attention, AttentionBackend, AttentionMetadata, AttentionPlan,  # noqa: F401
                                SlotTable, attention_kv_cache)
+from .layers.sampler import Sampler                                # noqa: F401
 
 
 
@@ -39,4 +41,4 @@ def shard_heads(num_qo_heads: int, num_kv_heads: int, tp_size: int, tp_rank: int
 
 __all__ = ["shard_heads", "Attention", "AttentionBackend", "AttentionMetadata", "AttentionPlan", "SlotTable",
            "attention_kv_cache", "KVCachePool", "store_kvcache", "CUDAGraph", "ForwardBatch", "ForwardMode",
-           "Sequence", "ops"]
+           "Sequence", "Sampler", "ops"]

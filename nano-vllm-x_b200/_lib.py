@@ -34,6 +34,7 @@ SIGNATURES = {
                             _i32, _i32, _i32, _i32, _i32, _f32, _i32, _i32, _vp]),
     "b200_qk_norm_rope_store": (_i32, [_vp, _i64, _vp, _vp, _vp, _f32, _vp, _i64, _i32, _vp, _i64, _vp, _i64,
                                        _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "b200_sample": (_i32, [_vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i64, _c.c_uint64, _c.c_uint64, _vp, _vp]),
     "b200_launch_count": (_i64, []),
     "b200_reset_launch_count": (None, []),
 }

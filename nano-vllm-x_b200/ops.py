@@ -210,6 +210,37 @@ def qk_norm_rope_store(qkv: torch.Tensor, positions: torch.Tensor, q_weight: tor
     _lib.check(rc, "b200_qk_norm_rope_store")
 
 
+# ---- (f-4) sampler tail -----------------------------------------------------------------------------
+_LOGIT_CODE = {torch.bfloat16: 0, torch.float32: 2}
+
+
+@torch.library.custom_op("b200attn::sample", mutates_args=(), device_types="cuda")
+def sample(logits: torch.Tensor, temperatures: torch.Tensor | None, min_ps: torch.Tensor | None,
+           top_ps: torch.Tensor | None, top_ks: torch.Tensor | None, noise: torch.Tensor | None,
+           seed: int, offset: int) -> torch.Tensor:
+    """layers/sampler.py:19-55 in one launch (see include/b200attn.h, f-4).  Argument order follows
+    ``Sampler.forward``.  ``noise`` = the Exp(1) tensor torch.multinomial would draw (parity), or None
+    for the in-kernel Philox stream keyed by (seed, offset)."""
+    _need_cuda(logits, temperatures, min_ps, top_ps, top_ks, noise)
+    assert logits.dim() == 2 and logits.stride(1) == 1 and logits.dtype in _LOGIT_CODE, "logits: [B, V] bf16 / fp32"
+    B, V = logits.shape
+    for t, dt in ((temperatures, torch.float32), (min_ps, torch.float32), (top_ps, torch.float32), (top_ks, torch.int64)):
+        assert t is None or (t.dtype == dt and t.numel() == B and t.is_contiguous())
+    assert noise is None or (noise.dtype == torch.float32 and noise.shape == logits.shape and noise.stride(1) == 1)
+    out = torch.empty((B,), dtype=torch.int64, device=logits.device)
+    lib = _lib.load()
+    rc = lib.b200_sample(logits.data_ptr(), logits.stride(0), _LOGIT_CODE[logits.dtype], B, V, _ptr(temperatures),
+                         _ptr(top_ks), _ptr(top_ps), _ptr(min_ps), _ptr(noise), 0 if noise is None else noise.stride(0),
+                         seed & 0xFFFFFFFFFFFFFFFF, offset & 0xFFFFFFFFFFFFFFFF, out.data_ptr(), _stream())
+    _lib.check(rc, "b200_sample")
+    return out
+
+
+@sample.register_fake
+def _(logits, temperatures, min_ps, top_ps, top_ks, noise, seed, offset):
+    return torch.empty((logits.shape[0],), dtype=torch.int64, device=logits.device)
+
+
 def launch_count() -> int:
     return int(_lib.load().b200_launch_count())
 
