@@ -227,6 +227,23 @@ class Layer(torch.nn.Module):
         return x + d
 
 
+def reference_sampler(logits, temps, min_ps, top_ps, top_ks):
+    """layers/sampler.py:38-55 with _apply_top_k_top_p (:58-90) and _apply_min_p (:93-106), restated (baseline arm)."""
+    x = logits.to(torch.float)
+    x.div_(temps.unsqueeze(1))
+    xs, idx = x.sort(dim=-1, descending=False)
+    kth = xs.gather(1, (xs.size(1) - top_ks).unsqueeze(1))
+    xs.masked_fill_(xs < kth, -float("inf"))
+    ps = xs.softmax(dim=-1).cumsum(dim=-1)
+    mask = ps <= 1 - top_ps.unsqueeze(1)
+    mask[:, -1] = False
+    xs.masked_fill_(mask, -float("inf"))
+    x = torch.empty_like(xs).scatter_(-1, idx, xs)
+    probs = torch.softmax(x, dim=-1)
+    x = x.masked_fill_(probs < min_ps.unsqueeze(1) * probs.max(dim=-1, keepdim=True).values, -float("inf"))
+    return torch.multinomial(torch.softmax(x, dim=-1, dtype=torch.float), 1).squeeze(-1)
+
+
 def rope(x, cos, sin):
     x1, x2 = x[..., : x.shape[-1] // 2], x[..., x.shape[-1] // 2:]
     return torch.cat([x1 * cos - x2 * sin, x2 * cos + x1 * sin], dim=-1).to(x.dtype)
@@ -282,6 +299,9 @@ def main():
                          "kv_indices / cached_kv_len, as RadixTree.match_prefix would at core/scheduler.py:67-74)")
     ap.add_argument("--fused-qk", action="store_true",
                     help="b200 backend only: q/k RMSNorm + RoPE + slot write as one kernel (SURVEY.md f-3)")
+    ap.add_argument("--sampler", default="torch", choices=["torch", "reference", "b200"],
+                    help="torch = softmax + multinomial; reference = the reference's sort-based Sampler restated "
+                         "(layers/sampler.py, what its engine really runs); b200 = b200attn::sample (SURVEY.md f-4)")
     a = ap.parse_args()
 
     import nanovllmx_b200 as pkg
@@ -344,14 +364,27 @@ def main():
 
         margins = []
 
+        b200_sampler = pkg.Sampler(seed=0) if a.sampler == "b200" else None
+
         def sample(hidden):
-            logits = (hidden @ model.lm_head.t()).float()
+            logits = hidden @ model.lm_head.t()
             if a.greedy:
-                top = torch.topk(logits, 2, dim=-1)
+                top = torch.topk(logits.float(), 2, dim=-1)
                 margins.append((top.values[:, 0] - top.values[:, 1]))
                 return top.indices[:, 0]
-            probs = torch.softmax(logits / 0.6, -1)
-            return torch.multinomial(probs, 1, generator=gen).squeeze(-1)
+            B = logits.shape[0]
+            if a.sampler == "torch":                 # bare softmax + multinomial (cheaper than what the reference runs)
+                probs = torch.softmax(logits.float() / 0.6, -1)
+                return torch.multinomial(probs, 1, generator=gen).squeeze(-1)
+            # what core/model_runner.py:191-219 sends for bench.py's SamplingParams(temperature=0.6): all four tensors,
+            # top_k = vocab_size, top_p = 1, min_p = 0, rebuilt from Python lists every step
+            temps = torch.tensor([0.6] * B, dtype=torch.float, device=dev)
+            min_ps = torch.tensor([0.0] * B, dtype=torch.float, device=dev)
+            top_ps = torch.tensor([1.0] * B, dtype=torch.float, device=dev)
+            top_ks = torch.tensor([cfg["vocab"]] * B, dtype=torch.long, device=dev)
+            if a.sampler == "b200":                  # one launch, no sort
+                return b200_sampler(logits, temps, min_ps, top_ps, top_ks)
+            return reference_sampler(logits, temps, min_ps, top_ps, top_ks)
 
         def run_eager(batch):
             ids = torch.tensor([t for s in batch.seqs for t in s.token_ids[s.cached_kv_len:]], dtype=torch.long, device=dev)
@@ -522,7 +555,7 @@ def main():
                    decode_steps=n_decode, prefill_s=t_prefill, decode_s=t_decode, generated_tokens=generated,
                    sum_max_tokens=sum(max_tokens), tok_s_reference_formula=sum(max_tokens) / wall,
                    tok_s_generated=generated / wall, graph_capture_s=t_cap, workload=a.workload, prefix_cache=a.prefix_cache,
-                   prefill_tokens_computed=prefill_tokens, prefix_warm_s=prefix_warm_s, greedy=a.greedy, fused_qk=model.fused,
+                   prefill_tokens_computed=prefill_tokens, prefix_warm_s=prefix_warm_s, greedy=a.greedy, fused_qk=model.fused, sampler=a.sampler,
                    prompt_tokens=sum(len(p) for p in prompts))
         if prof["n"]:
             # per decode step, host wall ms: building ids/positions, attention metadata (the hot path's host side), graph

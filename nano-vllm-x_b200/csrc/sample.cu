@@ -20,8 +20,6 @@ namespace b200 {
 namespace {
 
 constexpr int kSampleThreads = 1024;
-constexpr int kCopies = 8;                      // sub-histograms, selected by warp id, against same-bin contention
-constexpr float kFixScale = 1099511627776.0f;   // 2^40
 
 struct SampleParams {
   const void* logits;
@@ -35,6 +33,8 @@ struct SampleParams {
   int64_t noise_row_stride;
   uint64_t seed, offset;
   int64_t* out;
+  int limb_bits;       // histogram limb width, see radix_select
+  float fix_scale;     // 2^(2 * limb_bits - 1): fixed-point scale of a probability mass
 };
 
 template <typename T> struct KeyTraits;
@@ -98,80 +98,93 @@ __device__ __forceinline__ void block_max_pair(uint64_t& v, uint64_t* scratch) {
   v = m;
 }
 
-__device__ __forceinline__ uint64_t block_sum_u64(uint64_t v, uint64_t* scratch) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  __syncthreads();
-  if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
-  __syncthreads();
-  uint64_t s = 0;
-#pragma unroll
-  for (int w = 0; w < kSampleThreads / 32; ++w) s += scratch[w];
-  return s;
-}
-
 // ---- radix select -----------------------------------------------------------------------------------
+// Histograms use NATIVE 32-bit shared atomics only (a 64-bit shared atomicAdd compiles to a CAS spin loop) and are
+// striped by lane: cell (digit, lane) is touched by that lane alone within a warp, so neither bank conflicts nor
+// same-address serialisation occur however concentrated the digits are (the exponent byte of bf16 logits is).
+// A 64-bit weight is split into two limbs of `limb_bits` bits, each summed in its own 32-bit cell; a cell receives
+// at most ceil(V / 32) addends, so limb_bits = 32 - ceil(log2(ceil(V / 32))) (capped at 20) cannot overflow.
 struct SelectResult {
   uint32_t key;      // smallest key K with W(key <= K) > target; the largest present key if there is none
   uint64_t below;    // W(key < K)
   uint64_t equal;    // W(key == K)
+  uint64_t total;    // W(all active elements)
 };
 
 struct SelectSmem {
-  uint64_t hist[kCopies * 256];
+  uint64_t tot[256];
   uint64_t warp_tot[8];
   uint64_t red[kSampleThreads / 32];
-  uint64_t below, equal;
+  uint64_t below, equal, total;
   int digit, last_nonempty;
 };
 
+constexpr int kHistWords = 2 * 256 * 32;     // [limb][digit][lane] uint32 = 64 KiB of dynamic shared memory
+
 // Ascending weighted select over the elements for which elem(i, key, weight) returns true.  BITS = key width
-// (multiple of 8).  Every thread of the CTA must call it; every thread receives the result.
-template <int BITS, typename F>
-__device__ SelectResult radix_select(int V, uint64_t target, F elem, SelectSmem& sm) {
+// (multiple of 8).  The target is target_of(total weight), evaluated after the first pass, so a fraction of the
+// total needs no pass of its own.  Every thread of the CTA must call it; every thread receives the result.
+template <int BITS, bool WEIGHTED, typename F, typename G>
+__device__ SelectResult radix_select(int V, int limb_bits, F elem, G target_of, SelectSmem& sm, uint32_t* hist) {
   uint32_t prefix = 0;                       // digits chosen so far, right-aligned
-  uint64_t below_total = 0;
-  uint64_t eq = 0;
-  const int copy = (threadIdx.x >> 5) & (kCopies - 1);
+  uint64_t below_total = 0, eq = 0, total = 0, target = 0;
+  const int lane = threadIdx.x & 31;
+  const uint32_t limb_mask = (1u << limb_bits) - 1u;
 #pragma unroll 1
   for (int shift = BITS - 8; shift >= 0; shift -= 8) {
-    for (int t = threadIdx.x; t < kCopies * 256; t += kSampleThreads) sm.hist[t] = 0;
+    for (int t = threadIdx.x; t < (WEIGHTED ? kHistWords : kHistWords / 2); t += kSampleThreads) hist[t] = 0;
     if (threadIdx.x == 0) { sm.digit = -1; sm.last_nonempty = -1; }
     __syncthreads();
-    // per-thread run-length aggregation: consecutive equal digits (the common case on the exponent byte)
-    // cost one shared atomic per run instead of one per element
-    int run_digit = -1;
-    uint64_t run_w = 0;
     for (int i = threadIdx.x; i < V; i += kSampleThreads) {
       uint32_t key; uint64_t w;
       if (!elem(i, key, w)) continue;
       if (shift + 8 < BITS && (key >> (shift + 8)) != prefix) continue;
-      const int d = (key >> shift) & 0xFF;
-      if (d != run_digit) {
-        if (run_digit >= 0) atomicAdd(reinterpret_cast<unsigned long long*>(&sm.hist[copy * 256 + run_digit]), (unsigned long long)run_w);
-        run_digit = d;
-        run_w = 0;
+      const int cell = (((key >> shift) & 0xFF) << 5) | lane;
+      if (WEIGHTED) {
+        atomicAdd(&hist[cell], (uint32_t)w & limb_mask);
+        atomicAdd(&hist[256 * 32 + cell], (uint32_t)(w >> limb_bits));
+      } else {
+        atomicAdd(&hist[cell], 1u);
       }
-      run_w += w;
     }
-    if (run_digit >= 0) atomicAdd(reinterpret_cast<unsigned long long*>(&sm.hist[copy * 256 + run_digit]), (unsigned long long)run_w);
+    __syncthreads();
+    {   // bin totals: thread t sums a rotated quarter of the lanes of bin t / 4 (bank-conflict free)
+      const int bin = threadIdx.x >> 2, q = threadIdx.x & 3;
+      uint64_t lo = 0, hi = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int l = (q * 8 + j + bin) & 31;
+        lo += hist[(bin << 5) | l];
+        if (WEIGHTED) hi += hist[256 * 32 + ((bin << 5) | l)];
+      }
+      uint64_t t = lo + (hi << limb_bits);
+      t += __shfl_xor_sync(0xffffffffu, t, 1);
+      t += __shfl_xor_sync(0xffffffffu, t, 2);
+      if (q == 0) sm.tot[bin] = t;
+    }
     __syncthreads();
     // 256-bin inclusive scan by the first 8 warps, then locate the crossing bin
     uint64_t tot = 0, incl = 0;
     if (threadIdx.x < 256) {
-#pragma unroll
-      for (int c = 0; c < kCopies; ++c) tot += sm.hist[c * 256 + threadIdx.x];
+      tot = sm.tot[threadIdx.x];
       incl = tot;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const uint64_t y = __shfl_up_sync(0xffffffffu, incl, o);
-        if ((threadIdx.x & 31) >= o) incl += y;
+        if (lane >= o) incl += y;
       }
-      if ((threadIdx.x & 31) == 31) sm.warp_tot[threadIdx.x >> 5] = incl;
+      if (lane == 31) sm.warp_tot[threadIdx.x >> 5] = incl;
     }
     __syncthreads();
+    if (shift == BITS - 8) {                  // first pass: the grand total fixes the target
+      uint64_t all = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) all += sm.warp_tot[w];
+      total = all;
+      target = target_of(all);
+    }
     if (threadIdx.x < 256) {
-      for (int w = 0; w < (threadIdx.x >> 5); ++w) incl += sm.warp_tot[w];
+      for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) incl += sm.warp_tot[w];
       if (tot > 0) atomicMax(&sm.last_nonempty, (int)threadIdx.x);
       if (incl > target && incl - tot <= target) { sm.digit = threadIdx.x; sm.below = incl - tot; sm.equal = tot; }
     }
@@ -194,7 +207,7 @@ __device__ SelectResult radix_select(int V, uint64_t target, F elem, SelectSmem&
     eq = sm.equal;
     __syncthreads();
   }
-  return SelectResult{prefix, below_total, eq};
+  return SelectResult{prefix, below_total, eq, total};
 }
 
 // ---- the kernel ---------------------------------------------------------------------------------------
@@ -231,9 +244,13 @@ __device__ __forceinline__ uint64_t draw(const T* __restrict__ x, int V, bool ve
   using KT = KeyTraits<T>;
   float best_s = -INFINITY;
   int best_i = 0x7FFFFFFF;
+  float nxt[4];
+  load4(x, (int)threadIdx.x, V, vec, nxt);
   for (int g = threadIdx.x; g * 4 < V; g += kSampleThreads) {
     float raw[4];
-    load4(x, g, V, vec, raw);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) raw[j] = nxt[j];
+    load4(x, g + kSampleThreads, V, vec, nxt);     // next group's logits are in flight while this one is scored
     float lq[4];                                   // log2 of the Exp(1) noise
     if (nz) {
 #pragma unroll
@@ -265,6 +282,7 @@ template <typename T>
 __global__ void __launch_bounds__(kSampleThreads, 1) sample_kernel(SampleParams p) {
   using KT = KeyTraits<T>;
   __shared__ SelectSmem sm;
+  extern __shared__ uint32_t hist[];
   const int row = blockIdx.x;
   const int V = p.V;
   const T* __restrict__ x = reinterpret_cast<const T*>(p.logits) + (int64_t)row * p.row_stride;
@@ -305,32 +323,34 @@ __global__ void __launch_bounds__(kSampleThreads, 1) sample_kernel(SampleParams 
   }
   Cut c{0u, 0u, 0, need_minp ? min_p : -1.0f, KT::value(max_key), inv_t * kLog2e};
   // probability mass of element i relative to the row maximum, 2^-40 fixed point
-  auto mass = [&](int i) { return (uint64_t)__float2ull_rd(fast_exp2((to_float(x[i]) - c.maxv) * c.escale) * kFixScale); };
+  auto mass = [&](int i) { return (uint64_t)__float2ull_rd(fast_exp2((to_float(x[i]) - c.maxv) * c.escale) * p.fix_scale); };
 
   // top-k: the k-th largest key = the k-th smallest inverted key (sampler.py:67-73)
   if (need_k) {
     constexpr uint32_t kMask = KT::kBits == 32 ? 0xFFFFFFFFu : ((1u << (KT::kBits & 31)) - 1u);
     auto elem = [&](int i, uint32_t& key, uint64_t& w) { key = ~KT::key(x[i]) & kMask; w = 1; return true; };
-    c.kth_key = ~radix_select<KT::kBits>(V, (uint64_t)(k - 1), elem, sm).key & kMask;
+    auto tgt = [&](uint64_t) { return (uint64_t)(k - 1); };
+    c.kth_key = ~radix_select<KT::kBits, false>(V, 0, elem, tgt, sm, hist).key & kMask;
   }
 
   // top-p over what top-k kept (sampler.py:75-83)
   if (need_p) {
-    uint64_t z = 0;
-    for (int i = threadIdx.x; i < V; i += kSampleThreads)
-      if (KT::key(x[i]) >= c.kth_key) z += mass(i);
-    z = block_sum_u64(z, sm.red);
-    const double tgt = (double)(1.0f - top_p) * (double)z;
-    const uint64_t target = tgt <= 0.0 ? 0ull : (uint64_t)tgt;
+    // removed prefix = mass <= (1 - p) * Z, Z = mass of the top-k survivors = the first pass's grand total
+    uint64_t target = 0;
+    auto tgt = [&](uint64_t z) {
+      const double t = (double)(1.0f - top_p) * (double)z;
+      target = t <= 0.0 ? 0ull : (uint64_t)t;
+      return target;
+    };
     auto elem = [&](int i, uint32_t& key, uint64_t& w) {
       key = KT::key(x[i]);
       if (key < c.kth_key) return false;
       w = mass(i);
       return true;
     };
-    const SelectResult r = radix_select<KT::kBits>(V, target, elem, sm);
+    const SelectResult r = radix_select<KT::kBits, true>(V, p.limb_bits, elem, tgt, sm, hist);
     c.cut_key = r.key;
-    const uint64_t e_v = (uint64_t)__float2ull_rd(fast_exp2((KT::value(r.key) - c.maxv) * c.escale) * kFixScale);
+    const uint64_t e_v = (uint64_t)__float2ull_rd(fast_exp2((KT::value(r.key) - c.maxv) * c.escale) * p.fix_scale);
     uint64_t removed_ties = 0;
     if (e_v > 0) {
       const uint64_t ties = r.equal / e_v;
@@ -340,7 +360,8 @@ __global__ void __launch_bounds__(kSampleThreads, 1) sample_kernel(SampleParams 
     if (removed_ties > 0) {
       // ties at the cut leave lowest index first: the index of the (removed_ties + 1)-th tie is the first kept
       auto tie = [&](int i, uint32_t& key, uint64_t& w) { key = (uint32_t)i; w = 1; return KT::key(x[i]) == r.key; };
-      c.cut_idx = (int)radix_select<24>(V, removed_ties, tie, sm).key;
+      auto tgt2 = [&](uint64_t) { return removed_ties; };
+      c.cut_idx = (int)radix_select<24, false>(V, 0, tie, tgt2, sm, hist).key;
     }
   }
 
@@ -365,10 +386,23 @@ extern "C" int b200_sample(const void* logits, int64_t row_stride, int32_t logit
   if (B == 0) return 0;
   if (!logits || !out_ids) return fail("b200_sample: null pointer");
   if (row_stride < V || (noise && noise_row_stride < V)) return fail("b200_sample: row stride smaller than V");
-  SampleParams p{logits, row_stride, B, V, temperatures, top_ks, top_ps, min_ps, noise, noise_row_stride, seed, offset, out_ids};
+  if (logits_dtype != B200_DTYPE_BF16 && logits_dtype != B200_DTYPE_FP32)
+    return fail("b200_sample: logits dtype %d not supported (bf16, fp32)", logits_dtype);
+  int per_cell = (V + 31) / 32, lg = 0;
+  while ((1 << lg) < per_cell) ++lg;
+  const int limb_bits = 32 - lg < 20 ? 32 - lg : 20;
+  SampleParams p{logits, row_stride, B, V, temperatures, top_ks, top_ps, min_ps, noise, noise_row_stride, seed, offset, out_ids,
+                 limb_bits, ldexpf(1.0f, 2 * limb_bits - 1)};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (logits_dtype == B200_DTYPE_BF16) sample_kernel<__nv_bfloat16><<<B, kSampleThreads, 0, st>>>(p);
-  else if (logits_dtype == B200_DTYPE_FP32) sample_kernel<float><<<B, kSampleThreads, 0, st>>>(p);
-  else return fail("b200_sample: logits dtype %d not supported (bf16, fp32)", logits_dtype);
+  const size_t smem = kHistWords * sizeof(uint32_t);
+  {   // per device, cheap, not a stream operation (legal during graph capture)
+    if (cudaFuncSetAttribute(sample_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaFuncSetAttribute(sample_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return fail("b200_sample: cannot opt in to %zu bytes of shared memory", smem);
+    }
+  }
+  if (logits_dtype == B200_DTYPE_BF16) sample_kernel<__nv_bfloat16><<<B, kSampleThreads, smem, st>>>(p);
+  else sample_kernel<float><<<B, kSampleThreads, smem, st>>>(p);
   return check_launch("b200_sample");
 }
