@@ -64,3 +64,51 @@ def test_shard_heads_matches_reference_arithmetic():
             assert sorted(seen_q) == list(range(Hq))
     hq, hkv = pkg.shard_heads(16, 2, 4, 3)     # tp > Hkv: kv heads replicated (layers/linear.py:333-338)
     assert list(hkv) == [1] and list(hq) == [12, 13, 14, 15]
+
+
+def _wire_worker(rank, world, port, q):
+    """Rank 0 plays the scheduler: it encodes every step and broadcasts the bytes; every rank (the worker processes of
+    core/worker_client.py) decodes them and must end up with the batch rank 0 scheduled."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from importlib import import_module
+    import nanovllmx_b200 as pkg
+    from tests.test_wire import same_batch, scheduler_run
+    wire = import_module("nano-vllm-x_b200.core.wire")
+    enc, dec = wire.BatchEncoder(), wire.BatchDecoder()
+    ok, steps, prev_done = True, 0, []
+    for batch, done in scheduler_run(pkg, False, n=12, seed=3):     # every rank replays the same seeded schedule
+        n = torch.zeros(1, dtype=torch.int64)
+        if rank == 0:
+            for sid in prev_done:
+                enc.forget(sid)
+            msg = enc.encode(batch)
+            n[0] = len(msg)
+        prev_done = done
+        dist.broadcast(n, 0)
+        buf = torch.frombuffer(bytearray(msg), dtype=torch.uint8) if rank == 0 else torch.empty(int(n), dtype=torch.uint8)
+        dist.broadcast(buf, 0)
+        got = dec.decode(buf.numpy().tobytes())
+        try:
+            same_batch(got, batch)
+        except AssertionError:
+            ok = False
+        steps += 1
+    flags = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(flags, torch.tensor([int(ok)]))
+    if rank == 0:
+        q.put((all(int(f) for f in flags), steps))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_step_deltas_broadcast_to_two_workers():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_wire_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    ok, steps = q.get(timeout=180)
+    [p.join(timeout=120) for p in procs]
+    assert ok and steps > 20
+    assert [p.exitcode for p in procs] == [0, 0]
