@@ -115,6 +115,31 @@ __device__ __forceinline__ float exp2_fma(float x, float s, float b) {
   return y;
 }
 
+// Single-instruction ordered (asm volatile) forms + a warp barrier as a scheduling fence: the prefill softmax lays
+// out its FMA / MUFU / add / pack software pipeline with them (ptxas moves nothing across bar.warp.sync; left to
+// itself it spends every FMA as filler for the first MUFUs and then issues ~50 MUFU.EX2 back to back).
+__device__ __forceinline__ float fma_ordered(float x, float s, float b) {
+  float y;
+  asm volatile("fma.rn.f32 %0, %1, %2, %3;\n" : "=f"(y) : "f"(x), "f"(s), "f"(b));
+  return y;
+}
+__device__ __forceinline__ float exp2_ordered(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;\n" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float add_ordered(float a, float b) {
+  float y;
+  asm volatile("add.rn.f32 %0, %1, %2;\n" : "=f"(y) : "f"(a), "f"(b));
+  return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2_ordered(float lo, float hi) {
+  uint32_t y;
+  asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;\n" : "=r"(y) : "f"(hi), "f"(lo));
+  return y;
+}
+__device__ __forceinline__ void sched_fence() { asm volatile("bar.warp.sync 0xffffffff;\n" ::: "memory"); }
+
 __device__ __forceinline__ float fast_log2(float x) {
   float y;
   asm volatile("lg2.approx.ftz.f32 %0, %1;\n" : "=f"(y) : "f"(x));

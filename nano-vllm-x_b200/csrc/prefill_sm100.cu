@@ -364,6 +364,43 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   float s0 = 0.f, s1 = 0.f;
   // The O rescale sits AFTER the exponentials in its own (rare) branch: with the rescale ahead of them ptxas
   // hoists all 128 ex2 above it and spills 15 registers around the 32-register O chunk on the hot path.
+  if constexpr (!MASK) {
+    // Unmasked tiles (the common case): explicit software pipeline over the 128 elements.  The scale FMA runs
+    // kAhead elements ahead of its MUFU.EX2, the row-sum add and the bf16 pack kAhead elements behind it, so every
+    // MUFU (one per 8 clk per scheduler) has independent FMA-pipe work beside it.
+    constexpr int kAhead = 12;
+    uint32_t pw[64];
+#pragma unroll
+    for (int e = 0; e < kAhead; ++e)
+      sv[e >> 5][e & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[e >> 5][e & 31]), scale_log2, neg_m));
+#pragma unroll
+    for (int e = 0; e < 128 + kAhead; ++e) {
+      if ((e & 7) == 0) sched_fence();
+      if (e < 128) sv[e >> 5][e & 31] = __float_as_uint(exp2_ordered(__uint_as_float(sv[e >> 5][e & 31])));
+      if (e + kAhead < 128) {
+        const int f = e + kAhead;
+        sv[f >> 5][f & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[f >> 5][f & 31]), scale_log2, neg_m));
+      }
+      if (e >= kAhead) {
+        const int d = e - kAhead;
+        if (d & 1) {
+          s1 = add_ordered(s1, __uint_as_float(sv[d >> 5][d & 31]));
+          pw[d >> 1] = pack_bf16x2_ordered(__uint_as_float(sv[(d - 1) >> 5][(d - 1) & 31]), __uint_as_float(sv[d >> 5][d & 31]));
+          if ((d & 31) == 31) {
+            const int c = d >> 5;
+            tmem_st_32x32b_x16(tS + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&pw[c * 16]));   // P: packed bf16x2 over S
+            if (!rescale && (c == 1 || c == 3)) {     // hand P over in two halves: PV starts on the first
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(c == 1 ? bar_p0 : bar_p1);
+            }
+          }
+        } else {
+          s0 = add_ordered(s0, __uint_as_float(sv[d >> 5][d & 31]));
+        }
+      }
+    }
+  } else {
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     uint32_t pw[16];
@@ -381,6 +418,7 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       tc_fence_before();
       mbar_arrive(c == 1 ? bar_p0 : bar_p1);
     }
+  }
   }
   if (rescale) {                                    // O must carry the new scale before PV(j) accumulates into it
 #pragma unroll
