@@ -244,3 +244,66 @@ def test_decode_properties_long_context(pkg):
     K = k_cache[slots, h // 4].float(); V = v1[slots, h // 4].float()
     p = torch.softmax((K @ q[b, h].float()) * sm, 0)
     assert (o1[b, h] - p @ V).abs().max() <= 2e-2
+
+
+@pytest.mark.gpu
+def test_prefill_properties_full_bench_step(pkg):
+    """One prefill step of the WHOLE bench workload (BASELINE.json configs[2]: 256 prompts, 142 827 tokens,
+    Hq32/Hkv8, page 1, fragmented slots) — too large for the CPU oracle, so size-independent properties:
+    (1) the last query row of every sequence equals decode attention of that query over the same KV;
+    (2) V == const  =>  every output row == const;  (3) linear in V;
+    (4) three (sequence, token, head) rows spot-checked against a direct fp32 computation on the device."""
+    from oracle.paged_attention_oracle import bench_workload
+    plens = [len(p) for p in bench_workload()[0]]
+    assert len(plens) == 256 and sum(plens) == 142827          # reference README.md:99-100
+    Hq, Hkv, D = 32, 8, 128
+    c = dev(make_paged_case(plens, Hq, Hkv, q_lens=plens, seed=11))
+    T, B, sm = sum(plens), len(plens), D ** -0.5
+    ws = _ws(pkg, B, Hq, Hkv, D, T)
+    run = lambda v: pkg.ops.prefill(c["q"], c["k_cache"], v, c["qo_indptr"], c["kv_indptr"], c["kv_indices"],
+                                    c["last_page_len"], ws, 1, sm, True)
+    o1 = run(c["v_cache"])
+    assert torch.isfinite(o1.float()).all()
+    # (1) last row == decode
+    last_rows = (c["qo_indptr"][1:] - 1).long()
+    wsd = _ws(pkg, B, Hq, Hkv, D)
+    od = pkg.ops.decode(c["q"][last_rows].contiguous(), c["k_cache"], c["v_cache"], c["kv_indptr"], c["kv_indices"],
+                        c["last_page_len"], wsd, 1, sm)
+    assert (o1.view(T, Hq, D)[last_rows].float() - od.view(B, Hq, D).float()).abs().max() <= 1e-2
+    # (2) constant V
+    vc = torch.full_like(c["v_cache"], -0.5)
+    assert (run(vc).float() + 0.5).abs().max() <= 1e-2
+    # (3) linearity in V
+    v2 = torch.randn_like(c["v_cache"])
+    o2 = run(v2).float()
+    o12 = run((c["v_cache"].float() + v2.float()).to(torch.bfloat16)).float()
+    # four bf16 roundings (v1 + v2, o1, o2, o12), each half an ulp = 2^-9 relative: early rows attend to a handful of
+    # tokens, so |o| reaches 3..5 and the bound has to scale with the magnitude
+    bound = 1e-2 + 2.0 ** -8 * (o1.float().abs() + o2.abs() + 2 * o12.abs())
+    assert ((o12 - (o1.float() + o2)).abs() <= bound).all()
+    # (4) spot checks (first token, a middle token, last token of three sequences)
+    qo = c["qo_indptr"].cpu().numpy(); ip = c["kv_indptr"].cpu().numpy()
+    for s, frac, h in [(0, 0.0, 0), (100, 0.5, 13), (255, 1.0, 31)]:
+        n = int(qo[s + 1] - qo[s]); j = min(n - 1, int(frac * n))
+        slots = c["kv_indices"][ip[s]:ip[s] + j + 1].long()
+        K = c["k_cache"][slots, h // 4].float(); V = c["v_cache"][slots, h // 4].float()
+        p = torch.softmax((K @ c["q"][qo[s] + j, h].float()) * sm, 0)
+        assert (o1.view(T, Hq, D)[qo[s] + j, h].float() - p @ V).abs().max() <= 2e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("Hq,Hkv,ps", [(32, 8, 1), (4, 1, 16)])
+def test_prefill_prefix_split_invariance(pkg, Hq, Hkv, ps):
+    """Rows computed with a cached prefix (config 4's radix-hit path: only the suffix is new) equal the same rows of
+    a full prefill over the same slots, whatever the split point (tile-aligned or not)."""
+    L = [2048 + 200, 777, 130]
+    full = make_paged_case(L, Hq, Hkv, page_size=ps, q_lens=L, seed=21)
+    o_full = run_prefill(pkg, full).float()
+    qo = full["qo_indptr"]
+    for suffix in ([200, 77, 2], [1, 640, 129]):
+        part = dict(full)
+        part["qo_indptr"] = np.concatenate([[0], np.cumsum(suffix)]).astype(np.int32)
+        rows = np.concatenate([np.arange(qo[i + 1] - suffix[i], qo[i + 1]) for i in range(len(L))])
+        part["q"] = full["q"][torch.from_numpy(rows)].contiguous()
+        o_part = run_prefill(pkg, part).float()
+        assert (o_part - o_full[torch.from_numpy(rows).cuda()]).abs().max() <= 1e-2
