@@ -323,24 +323,28 @@ constexpr float kLazyTau = 8.0f;
 // One softmax step of one row (thread) over a 128-column S tile held in TMEM.
 // MASK is a template parameter so the (rare) masked tiles do not tax the common path with
 // predicated-off instructions (nvcc if-converts a runtime `if` around the element loop).
-template <bool MASK>
+template <bool MASK, int NCH = 4>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
                                              const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
                                              const uint32_t bar_p1) {
-  uint32_t sv[4][32];
+  // NCH (masked tiles only, tile-uniform): number of 32-column chunks of S that hold any valid column of this
+  // query tile.  The MMA issuer trims QK to N = 32*NCH and PV to K = 32*NCH, so chunks >= NCH are neither
+  // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
+  static_assert(MASK || NCH == 4, "only masked tiles are trimmed");
+  uint32_t sv[NCH][32];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+  for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
   tmem_wait_ld();
   if (MASK) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c)
+    for (int c = 0; c < NCH; ++c)
 #pragma unroll
       for (int e = 0; e < 32; ++e)
         if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
   }
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < NCH; ++c) {
 #pragma unroll
     for (int e = 0; e < 32; e += 4) {
       mx0 = fmaxf(mx0, __uint_as_float(sv[c][e]));
@@ -402,7 +406,7 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
     }
   } else {
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < NCH; ++c) {
     uint32_t pw[16];
 #pragma unroll
     for (int e = 0; e < 16; ++e) {
@@ -413,10 +417,12 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       pw[e] = pack_bf16x2(a, b);
     }
     tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
-    if (!rescale && (c == 1 || c == 3)) {           // hand P over in two halves: PV starts on the first
-      tmem_wait_st();                               // while the second is still in the exp unit
+    constexpr int kFirst = NCH > 1 ? 1 : 0;         // hand P over in two halves: PV starts on the first
+    if (!rescale && (c == kFirst || c == NCH - 1)) { // while the second is still in the exp unit
+      tmem_wait_st();
       tc_fence_before();
-      mbar_arrive(c == 1 ? bar_p0 : bar_p1);
+      if (c == kFirst) mbar_arrive(bar_p0);
+      if (c == NCH - 1) mbar_arrive(bar_p1);
     }
   }
   }
@@ -757,6 +763,9 @@ constexpr int kItemRing = 4;
 constexpr int kPlanThreads = 1024;
 constexpr int kPlanBuckets = 1024;
 constexpr int kWorkHeaderInts = 16;     // [0] work counter, [1] number of (sequence, tile) pairs
+// Dynamic shared memory: 2 Q tiles + 4-slot K/V ring + one 32 KiB tile the softmax warps stage output rows in.
+constexpr int kWsOffStage = kWsOffRing + kRing * kTileBytes2;   // persistent kernel only
+constexpr int kPersistSmem = kWsOffStage + kTileBytes2 + 1024;
 
 struct ItemDesc {
   int s, kvh, j0, Lq, Lkv, q0, page0, valid;
@@ -828,7 +837,9 @@ __global__ void __launch_bounds__(kPlanThreads, 1) prefill_plan_kernel(const Pre
 
 __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(const PrefillParams p, const int log2_g,
                                                                                int* __restrict__ work,
-                                                                               const int2* __restrict__ items) {
+                                                                               const int2* __restrict__ items,
+                                                                               const int flags) {
+  (void)flags;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem;
   __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing];
@@ -839,6 +850,17 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   const int G = 1 << log2_g;
   const int tok_per_tile = kTM >> log2_g;
   const int tok_per_cta = 2 * tok_per_tile;
+  // Trimmed last tiles: 32-column chunks of KV tile j that hold columns below the query tile's kv_hi.  Bench-shaped
+  // prompts (100..1024 tokens) own 1..8 KV tiles per item and the last one of each query tile is only
+  // partly valid (causal diagonal of a 32/64-token packed tile, ragged sequence end): QK, softmax and PV
+  // run on 32*nch columns instead of 128 (8-12 % of all chunk steps on the bench prompts).
+  // Compile-time switches, set from a same-box A/B on B200 (benchmarks/scripts/prefill_flags_ab.sh with these as run-time
+  // flags, profiles/r1_s38_prefill_flags_ab.txt; bench prompts Hq32 / uniform 16x4096 Hq32, fraction of bf16 peak):
+  //   none 0.303 / 0.633   trim 0.298 / 0.640   staged 0.319 / 0.650   lean_q 0.326 / 0.648   all three 0.291 / 0.670
+  // Trimming costs more than it saves on short prompts (four masked-softmax instances; the kernel is ~7000 SASS
+  // instructions and every extra hot path shows), so it stays off; dead branches are removed by the compiler.
+  constexpr bool trim = false, staged = true, lean_q = true;
+  auto chunks_of = [&](int kv_hi, int j) { return trim ? min(4, (kv_hi - j * kTN + 31) >> 5) : 4; };
 
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
@@ -970,39 +992,75 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
       if (g.J == 0) continue;
       const int kvh = d.kvh;
+      const uint32_t smem_q = smem + kWsOffQ, smem_ring = smem + kWsOffRing;
       // ---- Q: 256 packed rows ------------------------------------------------------------------------------
+      // Page ids of KV tile 0: issued here, consumed (slot arithmetic + smem store) only after the Q fill, so the
+      // load latency hides behind the 64 cp.async of Q instead of stalling the warp (the blocking form cost the
+      // loaders 25 % of their time on bench-shaped prompts: ncu source page, long-scoreboard stalls).
+      int pg_a = -1, pg_b = -1;
+      auto ldg_pages = [&](int tile) {
+        const int tok = tile * kTN + 4 * lane + 2 * lw;
+        pg_a = pg_b = -1;
+        if (tok < g.kv_hi_all) pg_a = __ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps));
+        if (tok + 1 < g.kv_hi_all) pg_b = __ldg(p.kv_indices + d.page0 + ((tok + 1) >> p.log2_ps));
+      };
+      auto put_slots = [&](int tile) {
+        const int tok = tile * kTN + 4 * lane + 2 * lw;
+        s_slots[tile & 1][lw][0][lane] = pg_a >= 0 ? (pg_a << p.log2_ps) + (tok & ps_mask) : -1;
+        s_slots[tile & 1][lw][1][lane] = pg_b >= 0 ? (pg_b << p.log2_ps) + ((tok + 1) & ps_mask) : -1;
+      };
+      ldg_pages(0);
       wait_or_flush(bar_qfree, (qn & 1) ^ 1);
       {
+        // 256 packed rows; this thread owns rows lrow0 + 4 i.  Row R -> (token j0 + R / G, head kvh G + R % G).
         const int rows_total = (g.toks0 + g.toks1) << log2_g;
+        if (lean_q && p.q_row_stride > 0 && p.q_row_stride < (1 << 22)) {
+          // lean form (32-bit offsets from the item's first row, ~8 instructions per cp.async; the general form
+          // below costs 29 and made the Q fill 60 % of all loader instructions on bench-shaped prompts)
+          const char* qbase = reinterpret_cast<const char*>(p.q + (int64_t)(d.q0 + d.j0) * p.q_row_stride +
+                                                            (int64_t)kvh * G * kTD + gc * 8);
+          const uint32_t stride_q = (uint32_t)p.q_row_stride * 2u, gmask = (uint32_t)G - 1u;
+          if (rows_total == 2 * kTM) {
+#pragma unroll 1
+            for (int io = 0; io < 64; io += 8) {
+              const uint32_t dbase = smem_q + io * 512 + (io >= 32 ? 16384 : 0);
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const uint32_t R = (uint32_t)lrow0 + 4u * (io + u);
+                const uint32_t off = (R >> log2_g) * stride_q + (R & gmask) * (kTD * 2);
+                cp_async_16(dbase + ((u & 1) ? dst_odd : dst_even) + u * 512, qbase + off, 16u);
+              }
+            }
+          } else {
+#pragma unroll 1
+            for (int io = 0; io < 64; io += 8) {
+              const uint32_t dbase = smem_q + io * 512 + (io >= 32 ? 16384 : 0);
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const uint32_t R = (uint32_t)lrow0 + 4u * (io + u);
+                const bool ok = R < (uint32_t)rows_total;
+                const uint32_t off = ok ? (R >> log2_g) * stride_q + (R & gmask) * (kTD * 2) : 0u;
+                cp_async_16(dbase + ((u & 1) ? dst_odd : dst_even) + u * 512, qbase + off, ok ? 16u : 0u);
+              }
+            }
+          }
+        } else {
 #pragma unroll 4
-        for (int i = 0; i < 256 / 4; ++i) {
-          const int R = lrow0 + 4 * i;                  // packed row 0..255
-          const bool ok = R < rows_total;
-          const int tok = d.j0 + (R >> log2_g), head = kvh * G + (R & (G - 1));
-          const __nv_bfloat16* src = p.q + (int64_t)(d.q0 + (ok ? tok : d.j0)) * p.q_row_stride +
-                                     (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
-          const int r = R & 127;
-          cp_async_16(smem + kWsOffQ + (R >> 7) * kTileBytes2 + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src,
-                      ok ? 16u : 0u);
+          for (int i = 0; i < 256 / 4; ++i) {
+            const int R = lrow0 + 4 * i;                  // packed row 0..255
+            const bool ok = R < rows_total;
+            const int tok = d.j0 + (R >> log2_g), head = kvh * G + (R & (G - 1));
+            const __nv_bfloat16* src = p.q + (int64_t)(d.q0 + (ok ? tok : d.j0)) * p.q_row_stride +
+                                       (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
+            const int r = R & 127;
+            cp_async_16(smem_q + (R >> 7) * kTileBytes2 + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src,
+                        ok ? 16u : 0u);
+          }
         }
       }
       rotate(bar_q);
       ++qn;
-      auto fetch_slots = [&](int tile) {
-        const int tok = tile * kTN + 4 * lane + 2 * lw;
-        int sa = -1, sb = -1;
-        if (tok < g.kv_hi_all) {
-          const int page = __ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps));
-          sa = (page << p.log2_ps) + (tok & ps_mask);
-        }
-        if (tok + 1 < g.kv_hi_all) {
-          const int page = __ldg(p.kv_indices + d.page0 + ((tok + 1) >> p.log2_ps));
-          sb = (page << p.log2_ps) + ((tok + 1) & ps_mask);
-        }
-        s_slots[tile & 1][lw][0][lane] = sa;
-        s_slots[tile & 1][lw][1][lane] = sb;
-      };
-      fetch_slots(0);
+      put_slots(0);
       const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)kvh * kTD + gc * 8);
       const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)kvh * kTD + gc * 8);
       const int N = 2 * g.J;
@@ -1018,11 +1076,11 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
             sl[4 * i] = v.x; sl[4 * i + 1] = v.y; sl[4 * i + 2] = v.z; sl[4 * i + 3] = v.w;
           }
           __syncwarp();
-          if (tile + 1 < g.J) fetch_slots(tile + 1);
+          if (tile + 1 < g.J) ldg_pages(tile + 1);          // consumed after the V fill of this tile
         }
         wait_or_flush(bar_empty(slot), (use & 1) ^ 1);
         const char* base = (n & 1) ? vbase : kbase;
-        const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2;
+        const uint32_t dst0 = smem_ring + slot * kTileBytes2;
         if ((tile + 1) * kTN <= g.kv_hi_all) {            // full tile: no zero-fill predicates
 #pragma unroll
           for (int i = 0; i < 32; ++i)
@@ -1036,20 +1094,24 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           }
         }
         rotate(bar_full(slot));
+        if ((n & 1) && tile + 1 < g.J) put_slots(tile + 1);
       }
     }
     flush();
   } else if (warp == 8) {
     // =================================== MMA issuer =======================================================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
+    constexpr uint32_t idesc_qk0 = make_idesc_bf16_f32(kTM, 0, 0, 0);             // N field filled per tile
     constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
     const uint64_t qdesc0 = make_smem_desc(smem + kWsOffQ, 16, 1024);
     const uint64_t kdesc0 = make_smem_desc(smem + kWsOffRing, 16, 1024);          // K tiles: K-major
     const uint64_t vdesc0 = make_smem_desc(smem + kWsOffRing, kBlkBytes, 1024);   // V tiles: MN-major
-    auto issue_qk = [&](int t, int f) {                 // f = running ring-fill index of the K tile
+    // f = running ring-fill index of the K tile; nch = 32-column chunks of S to produce (N = 32 * nch: the
+    // first N token rows of the K-major tile)
+    auto issue_qk = [&](int t, int f, int nch) {
       const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
       const uint64_t kd = kdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
+      const uint32_t idesc_qk = idesc_qk0 | ((uint32_t)(nch << 2) << 17);
 #pragma unroll
       for (int ks = 0; ks < kTD / 16; ++ks) {
         const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
@@ -1057,12 +1119,14 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       }
       umma_commit_elect(bar_s(t));
     };
-    auto issue_pv = [&](int t, int f, int half, bool acc) {   // f = running ring-fill index of the V tile
+    // f = running ring-fill index of the V tile; nks = 16-token K steps holding valid P columns (2 per chunk)
+    auto issue_pv = [&](int t, int f, int half, bool acc, int nks) {
       const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
 #pragma unroll
       for (int ks = half * 4; ks < half * 4 + 4; ++ks)
-        umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
-                      (acc || ks > 0));
+        if (ks < nks)
+          umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
+                        (acc || ks > 0));
     };
     int fillc = 0, qn = 0;
     int pc[2] = {0, 0};
@@ -1075,8 +1139,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_wait(bar_q, qn & 1);
       mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
       tc_fence_after();
-      if (g.nt0 > 0) issue_qk(0, base);
-      if (g.nt1 > 0) issue_qk(1, base);
+      if (g.nt0 > 0) issue_qk(0, base, chunks_of(g.kvhi0, 0));
+      if (g.nt1 > 0) issue_qk(1, base, chunks_of(g.kvhi1, 0));
       umma_commit_elect(bar_empty(base % kRing));                        // K(0) free once both QK(0) are done
       if (g.J == 1) umma_commit_elect(bar_qfree);                        // last QK of the item: Q may be refilled
       for (int j = 0; j < g.J; ++j) {
@@ -1086,13 +1150,15 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
           const int ntt = t ? g.nt1 : g.nt0;
+          const int kvhit = t ? g.kvhi1 : g.kvhi0;
           if (j < ntt) {
+            const int nks = 2 * chunks_of(kvhit, j);
             mbar_wait(bar_p(t, 0), pc[t] & 1);                           // first 64 columns of P_t(j) are in TMEM
             tc_fence_after();
-            issue_pv(t, fv, 0, j > 0);
+            issue_pv(t, fv, 0, j > 0, nks);
             mbar_wait(bar_p(t, 1), pc[t] & 1);                           // the rest
             tc_fence_after();
-            issue_pv(t, fv, 1, true);
+            issue_pv(t, fv, 1, true, nks);
             ++pc[t];
             if (j == ntt - 1) umma_commit_elect(bar_o(t));
           }
@@ -1102,7 +1168,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
               tc_fence_after();
               k_ready = true;
             }
-            issue_qk(t, fk);
+            issue_qk(t, fk, chunks_of(kvhit, j + 1));
           }
         }
         umma_commit_elect(bar_empty(fv % kRing));
@@ -1139,7 +1205,12 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
         if (need_mask) {
           const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
-          softmax_tile<true>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
+          switch (chunks_of(kv_hi, j)) {                              // tile-uniform
+            case 1: softmax_tile<true, 1>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+            case 2: softmax_tile<true, 2>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+            case 3: softmax_tile<true, 3>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+            default: softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+          }
         } else {
           softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
         }
@@ -1152,30 +1223,80 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         tc_fence_after();
       }
       const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
-      const bool row_ok = r < (tokst << log2_g);
-      __nv_bfloat16* dst = p.out + (int64_t)(d.q0 + (row_ok ? my_tok : d.j0)) * p.out_row_stride +
-                           (int64_t)(d.kvh * G + (r & (G - 1))) * kTD;
+      // Output rows go through shared memory so that every STG.128 of a warp writes four full 128-byte lines
+      // (8 lanes per row); straight from the TMEM layout (thread = row) a warp store touches 32 lines with 16 bytes
+      // each and the 8 softmax warps spent ~4000 LSU wavefront-cycles per item in the epilogue (14 % of their
+      // time on bench-shaped prompts).  Staging area, 4 KiB per warp (32 rows x 64 columns bf16, 16-byte pieces
+      // XOR-swizzled by row): the 7th operand tile, touched by nobody else.
+      const uint32_t stage = smem + kWsOffStage + (uint32_t)warp * 4096u;
+      const int rows_ok = tokst << log2_g;
+      const int rsub = lane >> 3, piece = lane & 7;
+      if (!has || !staged) {
+        // thread = row, straight from the TMEM layout.  Rows without any visible KV (Lkv == 0, or causal with
+        // Lkv < Lq) are zeros; with data this is the unstaged form kept for A/B measurements.
+        if (r < rows_ok) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + my_tok) * p.out_row_stride +
+                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+          if (!has) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t ov[32];
-        if (has) {
-          tmem_ld_32x32b_x32(tO + c * 32, ov);
-          tmem_wait_ld();
-        } else {
-#pragma unroll
-          for (int e = 0; e < 32; ++e) ov[e] = 0u;
-        }
-        if (row_ok) {
-#pragma unroll
-          for (int j8 = 0; j8 < 4; ++j8) {
-            uint4 w;
-            w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
-            w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
-            w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
-            w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
-            *reinterpret_cast<uint4*>(dst + c * 32 + j8 * 8) = w;
+            for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
           }
         }
+        if (has) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + (r < rows_ok ? my_tok : d.j0)) * p.out_row_stride +
+                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t ov[32];
+            tmem_ld_32x32b_x32(tO + c * 32, ov);
+            tmem_wait_ld();
+            if (r < rows_ok) {
+#pragma unroll
+              for (int j8 = 0; j8 < 4; ++j8) {
+                uint4 w;
+                w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+                w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+                w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+                w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+                dst[c * 4 + j8] = w;
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2 && has && staged; ++half) {
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          uint32_t ov[32];
+          tmem_ld_32x32b_x32(tO + (half * 2 + cc) * 32, ov);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j8 = 0; j8 < 4; ++j8) {
+            const uint32_t w0 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+            const uint32_t w1 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+            const uint32_t w2 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+            const uint32_t w3 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+            const uint32_t dst_s = stage + (uint32_t)lane * 128u + (uint32_t)(((cc * 4 + j8) ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst_s), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int row = 4 * k + rsub;                  // row of this warp's 32
+          uint4 w;
+          const uint32_t src_s = stage + (uint32_t)row * 128u + (uint32_t)((piece ^ (row & 7)) << 4);
+          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];\n" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(src_s) : "memory");
+          const int R = (warp & 3) * 32 + row;           // packed row of tile t
+          if (R < rows_ok) {
+            const int tok = d.j0 + t * tok_per_tile + (R >> log2_g);
+            __nv_bfloat16* dst = p.out + (int64_t)(d.q0 + tok) * p.out_row_stride +
+                                 (int64_t)(d.kvh * G + (R & (G - 1))) * kTD + half * 64 + piece * 8;
+            *reinterpret_cast<uint4*>(dst) = w;
+          }
+        }
+        __syncwarp();                                    // the next half (or item) overwrites the staging rows
       }
       tc_fence_before();   // O_t reads are complete before this group's next P arrive lets PV_t(0) overwrite O_t
     }
@@ -1227,7 +1348,7 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   if ((uintptr_t)workspace & 15) return fail("b200_prefill: workspace must be 16-byte aligned");
   static bool attr_p = false;
   if (!attr_p) {
-    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
+    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem);
     if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     attr_p = true;
   }
@@ -1236,8 +1357,9 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
   prefill_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, 2 * tok_per_tile, work, items, max_pairs);
   if (int rc = check_launch("b200_prefill(plan)")) return rc;
-  cudaError_t e = launch_pdl(prefill_sm100_persist_kernel, dim3(cached_num_sms()), dim3(kWsThreads), kWsSmem, st, p, log2_g, work,
-                             (const int2*)items);
+  const int trim = 0;   // reserved (run-time A/B flags of the kernel's compile-time switches)
+  cudaError_t e = launch_pdl(prefill_sm100_persist_kernel, dim3(cached_num_sms()), dim3(kWsThreads), kPersistSmem, st, p, log2_g, work,
+                             (const int2*)items, trim);
   if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): %s", cudaGetErrorString(e));
   return check_launch("b200_prefill(sm100 persist)");
 }
