@@ -1357,9 +1357,9 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
   prefill_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, 2 * tok_per_tile, work, items, max_pairs);
   if (int rc = check_launch("b200_prefill(plan)")) return rc;
-  const int trim = 0;   // reserved (run-time A/B flags of the kernel's compile-time switches)
+  const int flags = 0;  // reserved
   cudaError_t e = launch_pdl(prefill_sm100_persist_kernel, dim3(cached_num_sms()), dim3(kWsThreads), kPersistSmem, st, p, log2_g, work,
-                             (const int2*)items, trim);
+                             (const int2*)items, flags);
   if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): %s", cudaGetErrorString(e));
   return check_launch("b200_prefill(sm100 persist)");
 }
