@@ -857,8 +857,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   // prompts (100..1024 tokens) own 1..8 KV tiles per item and the last one of each query tile is only
   // partly valid (causal diagonal of a 32/64-token packed tile, ragged sequence end): QK, softmax and PV
   // run on 32*nch columns instead of 128 (8-12 % of all chunk steps on the bench prompts).
-  // Compile-time switches, set from a same-box A/B on B200 (benchmarks/scripts/prefill_flags_ab.sh with these as run-time
-  // flags, profiles/r1_s38_prefill_flags_ab.txt; bench prompts Hq32 / uniform 16x4096 Hq32, fraction of bf16 peak):
+  // Compile-time switches, set from a same-box A/B on B200 of a build that had them as run-time flags
+  // (profiles/r1_s38_prefill_flags_ab.txt; bench prompts Hq32 / uniform 16x4096 Hq32, fraction of bf16 peak):
   //   none 0.303 / 0.633   trim 0.298 / 0.640   staged 0.319 / 0.650   lean_q 0.326 / 0.648   all three 0.291 / 0.670
   // Trimming costs more than it saves on short prompts (four masked-softmax instances; the kernel is ~7000 SASS
   // instructions and every extra hot path shows), so it stays off; dead branches are removed by the compiler.
