@@ -146,17 +146,26 @@ def cpu_port_gbps(B_sample, L, Hq, Hkv, D, ps, steps=1, warmup=0):
     last = np.full(B_sample, ps, np.int32)
     new_slots = torch.from_numpy(np.array([int(perm[indptr[i + 1] - 1]) * ps + ps - 1 for i in range(B_sample)], np.int64))
 
+    # the plain-C port (pthreads, every host core; one work item per (sequence, KV head) so the query heads of a
+    # group share each K/V row): ~10x the numpy/torch restatement of the same arithmetic on the same cores
+    from oracle import c_oracle
+    qo = np.arange(B_sample + 1, dtype=np.int32)
+
     def step():
         orc.store_kvcache(k_new, v_new, k_cache, v_cache, new_slots)
-        return orc.decode_attention(q, k_cache, v_cache, indptr, perm, last, ps)
+        return c_oracle.paged_attention(q, k_cache, v_cache, qo, indptr, perm, last, ps, causal=False, threads=threads)
 
     for _ in range(warmup):
         step()
+    if steps is None:                       # default bench run: about 10 s of CPU work
+        t0 = time.perf_counter()
+        step()
+        steps = int(min(200, max(3, 10.0 / max(time.perf_counter() - t0, 1e-3))))
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / steps
-    return algorithmic_bytes(B_sample, L, Hq, Hkv, D, ps) / dt / 1e9, dt, threads
+    return algorithmic_bytes(B_sample, L, Hq, Hkv, D, ps) / dt / 1e9, dt, threads, steps
 
 
 def run_reference_arm(args):
@@ -165,8 +174,8 @@ def run_reference_arm(args):
         return
     # one host runs the WHOLE job's heads (the GPU arm shards them over the ranks; total work is fixed)
     Hq, Hkv, D = 32, 8, 128
-    val, dt, threads = cpu_port_gbps(args.cpu_sample_seqs, args.ctx, Hq, Hkv, D, args.page_size,
-                                     steps=max(args.steps, 1), warmup=args.warmup)
+    val, dt, threads, _ = cpu_port_gbps(args.cpu_sample_seqs, args.ctx, Hq, Hkv, D, args.page_size,
+                                        steps=max(args.steps, 1), warmup=args.warmup)
     sample = f"{args.cpu_sample_seqs} of {args.batch} sequences x {args.ctx} tokens, same shapes, per step"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
@@ -371,8 +380,7 @@ def run_b200_arm(args):
     # ---- (C) CPU baseline (rank 0, N=1 only) -----------------------------------------------------------
     cpu = None
     if rank == 0 and tp == 1 and not args.no_cpu_baseline:
-        n_pass = 12
-        val, dt, threads = cpu_port_gbps(args.cpu_sample_seqs, L, Hq, Hkv, D, ps, steps=n_pass, warmup=1)
+        val, dt, threads, n_pass = cpu_port_gbps(args.cpu_sample_seqs, L, Hq, Hkv, D, ps, steps=None, warmup=1)
         cpu = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{args.cpu_sample_seqs} of {B} sequences x {L} tokens (same shapes), {n_pass} passes of {dt:.2f} s"}
 

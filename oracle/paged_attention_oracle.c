@@ -92,7 +92,7 @@ void oracle_replay_graph_buffers(const int64_t* cached_kv_len, const int64_t* kv
 
 /* a-6 / a-7: layers/attention.py:332-373 semantics in fp32: gather, GQA head map h -> h/(Hq/Hkv),
  * softmax(scale * q.k) v, bottom-right causal (kv_pos <= Lkv - Lq + j).  bf16 in, fp32 out.
- * Work items (sequence, head) are handed to `threads` pthreads through an atomic counter (this image's
+ * Work items (sequence, KV head) are handed to `threads` pthreads through an atomic counter (this image's
  * gcc ships without libgomp) — all host threads, as the reported CPU baseline. */
 typedef struct {
   const uint16_t *q, *k_cache, *v_cache;
@@ -106,51 +106,77 @@ typedef struct {
 static void* attn_worker(void* arg) {
   attn_job* J = (attn_job*)arg;
   const int group = J->Hq / J->Hkv, D = J->D, ps = J->page_size;
-  float* s = NULL;
+  float* s = NULL; /* [group][lkv] scores, then weights */
+  float* qf = (float*)malloc((size_t)group * D * sizeof(float));
+  float* rowf = (float*)malloc((size_t)D * sizeof(float));
+  float* mx = (float*)malloc((size_t)group * sizeof(float));
   size_t cap = 0;
   for (;;) {
+    /* one item = (sequence, KV head): the `group` query heads that share it walk its K/V rows together, so every
+     * row is fetched and widened to fp32 once per group (GQA as the GPU kernels exploit it); the arithmetic of
+     * each head is unchanged: 8 partial sums in a fixed order for q.k, tokens in order for softmax and P.V */
     const int item = __atomic_fetch_add(&J->next, 1, __ATOMIC_RELAXED);
-    if (item >= J->B * J->Hq) break;
-    const int i = item / J->Hq, h = item % J->Hq;
+    if (item >= J->B * J->Hkv) break;
+    const int i = item / J->Hkv, kvh = item % J->Hkv;
     const int q0 = J->qo_indptr[i], lq = J->qo_indptr[i + 1] - q0;
     const int p0 = J->kv_indptr[i], np = J->kv_indptr[i + 1] - p0;
     const int lkv = np > 0 ? (np - 1) * ps + J->last_page_len[i] : 0;
-    const int kvh = h / group;
-    if ((size_t)lkv > cap) {
+    if ((size_t)lkv * group > cap) {
       free(s);
-      cap = (size_t)lkv;
+      cap = (size_t)lkv * group;
       s = (float*)malloc(cap * sizeof(float));
     }
     for (int j = 0; j < lq; ++j) {
-      float* o = J->out + ((int64_t)(q0 + j) * J->Hq + h) * D;
-      for (int d = 0; d < D; ++d) o[d] = 0.f;
+      float* o = J->out + ((int64_t)(q0 + j) * J->Hq + (int64_t)kvh * group) * D; /* group heads are adjacent */
+      for (int d = 0; d < group * D; ++d) o[d] = 0.f;
       int vis = J->causal ? lkv - lq + j + 1 : lkv;
       if (vis > lkv) vis = lkv;
       if (vis <= 0) continue;
-      const uint16_t* qr = J->q + ((int64_t)(q0 + j) * J->Hq + h) * D;
-      float m = -INFINITY;
+      const uint16_t* qr = J->q + ((int64_t)(q0 + j) * J->Hq + (int64_t)kvh * group) * D;
+      for (int d = 0; d < group * D; ++d) qf[d] = bf16_to_f32(qr[d]);
+      for (int g = 0; g < group; ++g) mx[g] = -INFINITY;
       for (int t = 0; t < vis; ++t) {
         const int64_t slot = (int64_t)J->kv_indices[p0 + t / ps] * ps + t % ps;
         const uint16_t* kr = J->k_cache + (slot * J->Hkv + kvh) * D;
-        float acc = 0.f;
-        for (int d = 0; d < D; ++d) acc += bf16_to_f32(qr[d]) * bf16_to_f32(kr[d]);
-        s[t] = acc * J->sm_scale;
-        if (s[t] > m) m = s[t];
+        for (int d = 0; d < D; ++d) rowf[d] = bf16_to_f32(kr[d]);
+        for (int g = 0; g < group; ++g) {
+          const float* qg = qf + (size_t)g * D;
+          float a8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          int d = 0;
+          for (; d + 8 <= D; d += 8)
+            for (int u = 0; u < 8; ++u) a8[u] += qg[d + u] * rowf[d + u];
+          float acc = ((a8[0] + a8[4]) + (a8[1] + a8[5])) + ((a8[2] + a8[6]) + (a8[3] + a8[7]));
+          for (; d < D; ++d) acc += qg[d] * rowf[d];
+          const float sc = acc * J->sm_scale;
+          s[(size_t)g * lkv + t] = sc;
+          if (sc > mx[g]) mx[g] = sc;
+        }
       }
-      float l = 0.f;
-      for (int t = 0; t < vis; ++t) {
-        s[t] = expf(s[t] - m);
-        l += s[t];
+      for (int g = 0; g < group; ++g) {
+        float* sg = s + (size_t)g * lkv;
+        float l = 0.f;
+        for (int t = 0; t < vis; ++t) {
+          sg[t] = expf(sg[t] - mx[g]);
+          l += sg[t];
+        }
+        for (int t = 0; t < vis; ++t) sg[t] = sg[t] / l;
       }
       for (int t = 0; t < vis; ++t) {
         const int64_t slot = (int64_t)J->kv_indices[p0 + t / ps] * ps + t % ps;
         const uint16_t* vr = J->v_cache + (slot * J->Hkv + kvh) * D;
-        const float w = s[t] / l;
-        for (int d = 0; d < D; ++d) o[d] += w * bf16_to_f32(vr[d]);
+        for (int d = 0; d < D; ++d) rowf[d] = bf16_to_f32(vr[d]);
+        for (int g = 0; g < group; ++g) {
+          const float w = s[(size_t)g * lkv + t];
+          float* og = o + (size_t)g * D;
+          for (int d = 0; d < D; ++d) og[d] += w * rowf[d];
+        }
       }
     }
   }
   free(s);
+  free(qf);
+  free(rowf);
+  free(mx);
   return NULL;
 }
 
