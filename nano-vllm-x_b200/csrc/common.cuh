@@ -36,6 +36,20 @@ inline int check_launch(const char* what) {
 
 int cached_num_sms();
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: set it once per (kernel, device),
+// not once per process (a process that launches on a second GPU would otherwise fail with "invalid configuration").
+// `done` is the caller's per-kernel flag array (one bit of state per device ordinal).
+template <typename K>
+inline cudaError_t ensure_dyn_smem(K kernel, int bytes, std::atomic<bool> (&done)[64]) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev >= 0 && dev < 64 && done[dev].load(std::memory_order_acquire)) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev].store(true, std::memory_order_release);
+  return e;
+}
+
 // Programmatic dependent launch (PDL): the kernel may become resident while the previous kernel on
 // the stream is still running; it must execute griddep_wait() before touching that kernel's output.
 // Capturable in CUDA graphs (becomes a programmatic dependency edge).

@@ -465,12 +465,9 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   p.subs = c.subs;
   p.scale_log2 = sm_scale * kLog2e;
 
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDecodeSmem);
-    if (e != cudaSuccess) return fail("b200_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_set = true;
-  }
+  static std::atomic<bool> attr_done[64];
+  if (cudaError_t e = ensure_dyn_smem(decode_kernel, kDecodeSmem, attr_done); e != cudaSuccess)
+    return fail("b200_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   cudaStream_t st = (cudaStream_t)stream;
   decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
   if (int rc = check_launch("b200_decode(stream)")) return rc;

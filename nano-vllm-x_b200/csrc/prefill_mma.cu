@@ -7,7 +7,6 @@
 // double buffered; q.K^T and p.V on mma.sync m16n8k16 with fp32 online softmax; bottom-right
 // aligned causal mask (query j sees kv positions <= Lkv - Lq + j).  The tcgen05/TMEM kernel
 // (prefill_sm100.cu) supersedes it for the shapes it covers.
-#include <cstdlib>
 
 #include "common.cuh"
 #include "prefill_params.cuh"
@@ -237,12 +236,9 @@ static int ilog2_exact_p(int x) {
 }
 
 int launch_prefill_mma(const PrefillParams& p, int total_q, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(prefill_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPrefillSmem);
-    if (e != cudaSuccess) return fail("b200_prefill: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_set = true;
-  }
+  static std::atomic<bool> attr_done[64];
+  if (cudaError_t e = ensure_dyn_smem(prefill_mma_kernel, kPrefillSmem, attr_done); e != cudaSuccess)
+    return fail("b200_prefill: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   const int max_q_tiles = total_q / kQTile + p.B;  // >= sum_i ceil(Lq_i / 64)
   prefill_mma_kernel<<<dim3(max_q_tiles, p.Hq), kPWarps * 32, kPrefillSmem, st>>>(p);
   return check_launch("b200_prefill(mma)");
@@ -292,9 +288,9 @@ extern "C" int b200_prefill(const void* q, int64_t q_row_stride, const void* k_c
   p.kv_slot_stride = kv_slot_stride;
   p.B = B; p.Hq = Hq; p.Hkv = Hkv; p.group = Hq / Hkv; p.log2_ps = log2_ps; p.causal = causal ? 1 : 0;
   p.scale_log2 = sm_scale * kLog2e;
-  // tcgen05/TMEM kernel for every shape it covers; the mma.sync kernel only for GQA groups that do
-  // not pack into a 128-row tile.  B200ATTN_PREFILL=mma forces the latter (A/B measurements only).
-  static const bool force_mma = [] { const char* e = getenv("B200ATTN_PREFILL"); return e && e[0] == 'm'; }();
-  if (!force_mma && prefill_sm100_supports(p.group)) return launch_prefill_sm100(p, total_q, workspace, workspace_bytes, (cudaStream_t)stream);
+  // One kernel per shape class, decided by the shape alone (no environment switches): the tcgen05/TMEM kernel for
+  // every GQA group that packs into a 128-row tile (1, 2, 4, 8, ...: all Qwen3 models but the 14B), the mma.sync
+  // kernel for the others (group 3, 5 (Qwen3-14B: 40/8), 6, 7).
+  if (prefill_sm100_supports(p.group)) return launch_prefill_sm100(p, total_q, workspace, workspace_bytes, (cudaStream_t)stream);
   return launch_prefill_mma(p, total_q, (cudaStream_t)stream);
 }

@@ -15,8 +15,6 @@
 // Double-buffered: tile t+1 streams in while tile t is on the tensor cores.
 // O lives in TMEM across the KV loop; a row is rescaled in place (tcgen05.ld/st) only when its
 // running max moves.
-#include <cstdlib>
-
 #include "common.cuh"
 #include "prefill_params.cuh"
 #include "sm100.cuh"
@@ -30,272 +28,9 @@ constexpr int kTM = 128;                       // packed query rows per CTA
 constexpr int kTN = 128;                       // KV tokens per tile
 constexpr int kBlkBytes = 128 * 128;           // one [128 rows x 64 elem] swizzled block = 16 KiB
 constexpr int kTileBytes2 = 2 * kBlkBytes;     // a full [128 x 128] bf16 operand tile = 32 KiB
-constexpr int kOffQ = 0;
-constexpr int kOffP = kOffQ + kTileBytes2;
-constexpr int kOffK = kOffP + kTileBytes2;     // 2 stages
-constexpr int kOffV = kOffK + 2 * kTileBytes2; // 2 stages
-constexpr int kSm100Smem = kOffV + 2 * kTileBytes2 + 1024;  // + alignment slack = 193 KiB
-constexpr int kTmemCols = 256;                 // S: [0,128)  O: [128,256)
-
-
-__global__ void __launch_bounds__(128, 1) prefill_sm100_kernel(const PrefillParams p, const int log2_g) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ int s_scan[5];
-  __shared__ int s_loc[2];
-  __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[2];
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int kvh = blockIdx.y;
-  const int G = 1 << log2_g;
-  const int tok_per_tile = kTM >> log2_g;
-
-  // ---- locate (sequence, q tile) -------------------------------------------------------------------
-  {
-    const int target = blockIdx.x;
-    int carry = 0;
-    bool found = false;
-    for (int base = 0; base < p.B; base += 128) {
-      const int i = base + tid;
-      int t = 0;
-      if (i < p.B) t = (p.qo_indptr[i + 1] - p.qo_indptr[i] + tok_per_tile - 1) / tok_per_tile;
-      int blk;
-      const int incl = block_inclusive_scan<128>(t, s_scan, &blk) + carry;
-      const int excl = incl - t;
-      if (t > 0 && excl <= target && target < incl) {
-        s_loc[0] = i;
-        s_loc[1] = target - excl;
-      }
-      carry += blk;
-      if (carry > target) {
-        found = true;
-        break;
-      }
-    }
-    __syncthreads();
-    if (!found) return;
-  }
-  const int s = s_loc[0];
-  const int q0 = p.qo_indptr[s];
-  const int Lq = p.qo_indptr[s + 1] - q0;
-  const int j0 = s_loc[1] * tok_per_tile;
-  const int toks_here = min(tok_per_tile, Lq - j0);
-  const int rows_here = toks_here << log2_g;
-  const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
-  const int page0 = p.kv_indptr[s];
-  const int ps_mask = (1 << p.log2_ps) - 1;
-  int kv_hi = Lkv;
-  if (p.causal) kv_hi = min(Lkv, Lkv - Lq + j0 + toks_here);
-  if (kv_hi < 0) kv_hi = 0;
-  const int n_tiles = (kv_hi + kTN - 1) / kTN;
-
-  const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B atoms need 1024-byte alignment
-  const uint32_t bar_s = smem_u32(&s_bar[0]), bar_o = smem_u32(&s_bar[1]);
-
-  // ---- one-time setup: barriers + TMEM ---------------------------------------------------------------
-  if (tid == 0) {
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
-    fence_mbar_init();
-  }
-  if (warp == 0) {
-    tmem_alloc(smem_u32(&s_tmem), kTmemCols);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = s_tmem;
-  const uint32_t tmem_lane = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's 32-lane quadrant
-  const uint32_t tS = tmem_lane, tO = tmem_lane + kTN;
-
-  // ---- loaders (all 128 threads; half-warp = one 256-byte row) --------------------------------------
-  const int gc = tid & 15, lrow0 = tid >> 4;           // global 16-byte chunk 0..15; rows lrow0 + 8*i
-  const uint32_t chunk_off = (uint32_t)(gc >> 3) * kBlkBytes;
-  const int c8 = gc & 7;
-  {
-#pragma unroll
-    for (int i = 0; i < kTM / 8; ++i) {
-      const int r = lrow0 + 8 * i;
-      const bool ok = r < rows_here;
-      const int tok = j0 + (r >> log2_g), head = kvh * G + (r & (G - 1));
-      const __nv_bfloat16* src = p.q + (int64_t)(q0 + (ok ? tok : j0)) * p.q_row_stride + (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
-      cp_async_16(smem + kOffQ + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src, ok ? 16u : 0u);
-    }
-  }
-  auto issue_kv = [&](int tile) {
-    const uint32_t kst = smem + kOffK + (tile & 1) * kTileBytes2 + chunk_off;
-    const uint32_t vst = smem + kOffV + (tile & 1) * kTileBytes2 + chunk_off;
-#pragma unroll
-    for (int i = 0; i < kTN / 8; ++i) {
-      const int r = lrow0 + 8 * i;
-      const int tok = tile * kTN + r;
-      const bool ok = tok < kv_hi;
-      int64_t off = (int64_t)kvh * kTD + gc * 8;
-      if (ok) {
-        const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
-        off += ((int64_t)(page << p.log2_ps) + (tok & ps_mask)) * p.kv_slot_stride;
-      }
-      const uint32_t o = r * 128 + ((c8 ^ (r & 7)) << 4);
-      cp_async_16(kst + o, p.k_cache + off, ok ? 16u : 0u);
-      cp_async_16(vst + o, p.v_cache + off, ok ? 16u : 0u);
-    }
-  };
-  if (n_tiles > 0) issue_kv(0);
-  cp_async_commit();
-
-  // ---- per-row state ------------------------------------------------------------------------------------
-  const int r = tid;                                              // my packed row == my TMEM lane
-  const int my_tok = j0 + (r >> log2_g);
-  const int lim = p.causal ? (Lkv - Lq + my_tok) : (Lkv - 1);     // last visible kv position
-  const int lim0 = p.causal ? (Lkv - Lq + j0) : (Lkv - 1);        // smallest limit in the tile
-  float m_run = -INFINITY, l_run = 0.f;
-
-  constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);   // A K-major, B K-major
-  constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);   // A K-major, B MN-major (V)
-  uint32_t phase_s = 0, phase_o = 0;
-
-  for (int tile = 0; tile < n_tiles; ++tile) {
-    if (tile + 1 < n_tiles) issue_kv(tile + 1);
-    cp_async_commit();
-    cp_async_wait<1>();            // my chunks of tile `tile` (and Q) have landed
-    fence_proxy_async_smem();      // ... and are visible to the tensor-core (async) proxy
-    __syncthreads();
-
-    const uint32_t kst = smem + kOffK + (tile & 1) * kTileBytes2;
-    const uint32_t vst = smem + kOffV + (tile & 1) * kTileBytes2;
-
-    // ---- S = Q K^T ---------------------------------------------------------------------------------------
-    if (tid == 0) {
-      tc_fence_after();
-#pragma unroll
-      for (int ks = 0; ks < kTD / 16; ++ks) {
-        const uint32_t koff = (uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32;
-        umma_ss(tmem, make_smem_desc(smem + kOffQ + koff, 16, 1024), make_smem_desc(kst + koff, 16, 1024), idesc_qk,
-                ks > 0);
-      }
-      umma_commit(bar_s);
-    }
-    __syncwarp();
-    mbar_wait(bar_s, phase_s);
-    phase_s ^= 1;
-    tc_fence_after();
-
-    // ---- softmax on my row --------------------------------------------------------------------------------
-    const int kv0 = tile * kTN;
-    const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
-    uint32_t sv[4][32];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
-    tmem_wait_ld();
-    float mx = -INFINITY;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        float x = __uint_as_float(sv[c][j]) * p.scale_log2;
-        if (need_mask) {
-          const int kvp = kv0 + c * 32 + j;
-          if (kvp > lim || kvp >= kv_hi) x = -INFINITY;
-        }
-        sv[c][j] = __float_as_uint(x);
-        mx = fmaxf(mx, x);
-      }
-    }
-    const float m_new = fmaxf(m_run, mx);
-    const float sub = (m_new == -INFINITY) ? 0.f : m_new;
-    const float alpha = fast_exp2(m_run - sub);
-    float sum = 0.f;
-    // P -> bf16 -> swizzled K-major smem tile (A operand of the PV MMA)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-#pragma unroll
-      for (int j8 = 0; j8 < 4; ++j8) {
-        uint32_t w[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float a = fast_exp2(__uint_as_float(sv[c][j8 * 8 + 2 * e]) - sub);
-          const float b = fast_exp2(__uint_as_float(sv[c][j8 * 8 + 2 * e + 1]) - sub);
-          sum += a + b;
-          w[e] = pack_bf16x2(a, b);
-        }
-        const int chunk = c * 4 + j8;                   // 16-byte chunk 0..15 along the token (K) axis
-        const uint32_t dst = smem + kOffP + (uint32_t)(chunk >> 3) * kBlkBytes + r * 128 + (((chunk & 7) ^ (r & 7)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
-      }
-    }
-    l_run = l_run * alpha + sum;
-    // ---- rescale my O row in TMEM if the running max moved (PV of the previous tile has completed) ----------
-    if (tile > 0 && __any_sync(0xffffffffu, m_new != m_run)) {
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t ov[32];
-        tmem_ld_32x32b_x32(tO + c * 32, ov);
-        tmem_wait_ld();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) ov[j] = __float_as_uint(__uint_as_float(ov[j]) * alpha);
-        tmem_st_32x32b_x32(tO + c * 32, ov);
-      }
-      tmem_wait_st();
-    }
-    m_run = m_new;
-    fence_proxy_async_smem();      // P (generic-proxy stores) -> async proxy
-    tc_fence_before();
-    __syncthreads();
-
-    // ---- O += P V --------------------------------------------------------------------------------------------
-    if (tid == 0) {
-      tc_fence_after();
-#pragma unroll
-      for (int ks = 0; ks < kTN / 16; ++ks) {
-        const uint32_t poff = (uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32;   // 16 tokens along K of P
-        const uint32_t voff = (uint32_t)ks * 16 * 128;                                      // 16 token rows of V
-        umma_ss(tmem + kTN, make_smem_desc(smem + kOffP + poff, 16, 1024), make_smem_desc(vst + voff, kBlkBytes, 1024),
-                idesc_pv, (tile > 0 || ks > 0));
-      }
-      umma_commit(bar_o);
-    }
-    __syncwarp();
-    mbar_wait(bar_o, phase_o);     // K/V stage, P tile and O are free/complete again
-    phase_o ^= 1;
-    tc_fence_after();
-  }
-  cp_async_wait<0>();
-
-  // ---- epilogue: O / l -> bf16 -> global ------------------------------------------------------------------------
-  const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
-  const bool row_ok = r < rows_here;
-  __nv_bfloat16* dst = p.out + (int64_t)(q0 + (row_ok ? my_tok : j0)) * p.out_row_stride + (int64_t)(kvh * G + (r & (G - 1))) * kTD;
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    uint32_t ov[32];
-    if (n_tiles > 0) {
-      tmem_ld_32x32b_x32(tO + c * 32, ov);
-      tmem_wait_ld();
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) ov[j] = 0u;
-    }
-    if (row_ok) {
-#pragma unroll
-      for (int j8 = 0; j8 < 4; ++j8) {
-        uint4 w;
-        w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
-        w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
-        w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
-        w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
-        *reinterpret_cast<uint4*>(dst + c * 32 + j8 * 8) = w;
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, kTmemCols);
-}
-
 
 // =====================================================================================================
-// Stage 2: warp-specialised, two query tiles per CTA in ping-pong (the production path).
+// Warp-specialised pipeline, two query tiles per CTA in ping-pong.
 //
 //   warps 0-3   softmax group 0  (rows   0..127 of the CTA's 256 packed rows; thread == row == TMEM lane)
 //   warps 4-7   softmax group 1  (rows 128..255)
@@ -317,7 +52,6 @@ constexpr int kWsLoaders = 64;
 constexpr int kRing = 4;
 constexpr int kWsOffQ = 0;                           // 2 x 32 KiB
 constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
-constexpr int kWsSmem = kWsOffRing + kRing * kTileBytes2 + 1024;
 constexpr float kLazyTau = 8.0f;
 
 // One softmax step of one row (thread) over a 128-column S tile held in TMEM.
@@ -444,305 +178,9 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   l_run = l_run * alpha + (s0 + s1);
 }
 
-__global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_ws_kernel(const PrefillParams p, const int log2_g) {
-  extern __shared__ uint8_t smem_raw[];
-  __shared__ int s_scan[kWsThreads / 32 + 1];
-  __shared__ int s_loc[2];
-  __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[1 + 2 * kRing + 8];
-  __shared__ __align__(16) int s_slots[2][2][2][32];   // [tile parity][loader warp][row parity][i]
-
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int kvh = blockIdx.y;
-  const int G = 1 << log2_g;
-  const int tok_per_tile = kTM >> log2_g;        // tokens per 128-row tile
-  const int tok_per_cta = 2 * tok_per_tile;
-
-  {
-    const int target = gridDim.x - 1 - blockIdx.x;   // heaviest (latest) query tiles of a sequence launch first
-    int carry = 0;
-    bool found = false;
-    for (int base = 0; base < p.B; base += kWsThreads) {
-      const int i = base + tid;
-      int t = 0;
-      if (i < p.B) t = (p.qo_indptr[i + 1] - p.qo_indptr[i] + tok_per_cta - 1) / tok_per_cta;
-      int blk;
-      const int incl = block_inclusive_scan<kWsThreads>(t, s_scan, &blk) + carry;
-      const int excl = incl - t;
-      if (t > 0 && excl <= target && target < incl) {
-        s_loc[0] = i;
-        s_loc[1] = target - excl;
-      }
-      carry += blk;
-      if (carry > target) {
-        found = true;
-        break;
-      }
-    }
-    __syncthreads();
-    if (!found) return;
-  }
-  const int s = s_loc[0];
-  const int q0 = p.qo_indptr[s];
-  const int Lq = p.qo_indptr[s + 1] - q0;
-  const int j0 = s_loc[1] * tok_per_cta;
-  const int Lkv = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
-  const int toks0 = max(0, min(tok_per_tile, Lq - j0)), toks1 = max(0, min(tok_per_tile, Lq - j0 - tok_per_tile));
-  int kvhi0 = p.causal ? min(Lkv, Lkv - Lq + j0 + toks0) : Lkv;
-  int kvhi1 = p.causal ? min(Lkv, Lkv - Lq + j0 + tok_per_tile + toks1) : Lkv;
-  if (kvhi0 < 0 || toks0 == 0) kvhi0 = 0;
-  if (kvhi1 < 0 || toks1 == 0) kvhi1 = 0;
-  const int nt0 = (kvhi0 + kTN - 1) / kTN, nt1 = (kvhi1 + kTN - 1) / kTN;
-  const int J = max(nt0, nt1);
-  const int kv_hi_all = max(kvhi0, kvhi1);
-
-  const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar0 = smem_u32(&s_bar[0]);
-  const uint32_t bar_q = bar0;
-  auto bar_full = [&](int slot) { return bar0 + 8u * (1 + slot); };
-  auto bar_empty = [&](int slot) { return bar0 + 8u * (1 + kRing + slot); };
-  auto bar_s = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + t); };
-  auto bar_p = [&](int t, int half) { return bar0 + 8u * (1 + 2 * kRing + 2 + 2 * t + half); };
-  auto bar_o = [&](int t) { return bar0 + 8u * (1 + 2 * kRing + 6 + t); };
-
-  if (tid == 0) {
-    mbar_init(bar_q, kWsLoaders);
-    for (int i = 0; i < kRing; ++i) {
-      mbar_init(bar_full(i), kWsLoaders);
-      mbar_init(bar_empty(i), 1);
-    }
-    for (int t = 0; t < 2; ++t) {
-      mbar_init(bar_s(t), 1);
-      mbar_init(bar_p(t, 0), 128);
-      mbar_init(bar_p(t, 1), 128);
-      mbar_init(bar_o(t), 1);
-    }
-    fence_mbar_init();
-  }
-  if (warp == 0) {
-    tmem_alloc(smem_u32(&s_tmem), 512);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = s_tmem;
-
-  if (warp >= 11) {
-    // spare warp of the third warpgroup: only takes part in the register hand-over
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-  } else if (warp >= 9) {
-    // =================================== loaders ==========================================================
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    const int lt = tid - 9 * 32;                    // 0..63
-    const int gc = lt & 15, lrow0 = lt >> 4;        // rows lrow0 + 4*i
-    const uint32_t chunk_off = (uint32_t)(gc >> 3) * kBlkBytes;
-    const int c8 = gc & 7;
-    const int page0 = p.kv_indptr[s];
-    const int ps_mask = (1 << p.log2_ps) - 1;
-    const int rows_total = (toks0 + toks1) << log2_g;
-#pragma unroll 4
-    for (int i = 0; i < 256 / 4; ++i) {
-      const int R = lrow0 + 4 * i;                  // packed row 0..255
-      const bool ok = R < rows_total;
-      const int tok = j0 + (R >> log2_g), head = kvh * G + (R & (G - 1));
-      const __nv_bfloat16* src = p.q + (int64_t)(q0 + (ok ? tok : j0)) * p.q_row_stride + (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
-      const int r = R & 127;
-      cp_async_16(smem + kWsOffQ + (R >> 7) * kTileBytes2 + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src, ok ? 16u : 0u);
-    }
-    cp_async_commit();
-    const int N = 2 * J;
-    // Page-table lookups are taken off the critical path: ONE TILE AHEAD, lane l of loader warp w fetches
-    // the slots of rows 4l+2w and 4l+2w+1 (coalesced) and parks them in shared memory; a fill then picks up
-    // its 32 row slots with 8 broadcast LDS.128.  The fill loop itself is ~7 instructions per 16-byte
-    // cp.async (the first version spent ~70 and made the loaders the bottleneck of the whole kernel).
-    const int lane = tid & 31, lw = warp - 9;
-    const int hrow = lane >> 4;
-    auto fetch_slots = [&](int tile) {
-      const int tok = tile * kTN + 4 * lane + 2 * lw;
-      int sa = -1, sb = -1;
-      if (tok < kv_hi_all) {
-        const int page = __ldg(p.kv_indices + page0 + (tok >> p.log2_ps));
-        sa = (page << p.log2_ps) + (tok & ps_mask);
-      }
-      if (tok + 1 < kv_hi_all) {
-        const int page = __ldg(p.kv_indices + page0 + ((tok + 1) >> p.log2_ps));
-        sb = (page << p.log2_ps) + ((tok + 1) & ps_mask);
-      }
-      s_slots[tile & 1][lw][0][lane] = sa;
-      s_slots[tile & 1][lw][1][lane] = sb;
-    };
-    if (J > 0) fetch_slots(0);
-    const uint32_t stride_b = (uint32_t)(p.kv_slot_stride * 2);   // bytes between token slots (< 4 GiB)
-    const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)kvh * kTD + gc * 8);
-    const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)kvh * kTD + gc * 8);
-    // row r = lrow0 + 4i: byte offset r*128 = lrow0*128 + i*512; swizzle term depends on i's parity only
-    const uint32_t dst_even = chunk_off + lrow0 * 128 + ((c8 ^ lrow0) << 4);
-    const uint32_t dst_odd = chunk_off + lrow0 * 128 + ((c8 ^ (lrow0 + 4)) << 4);
-    int sl[32];
-    for (int n = 0; n < N; ++n) {
-      const int slot = n % kRing, use = n / kRing;
-      const int tile = n >> 1;
-      if ((n & 1) == 0) {
-        __syncwarp();
-        const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int4 v = src[i];
-          sl[4 * i] = v.x; sl[4 * i + 1] = v.y; sl[4 * i + 2] = v.z; sl[4 * i + 3] = v.w;
-        }
-        __syncwarp();
-        if (tile + 1 < J) fetch_slots(tile + 1);
-      }
-      mbar_wait(bar_empty(slot), (use & 1) ^ 1);
-      const char* base = (n & 1) ? vbase : kbase;
-      const uint32_t dst0 = smem + kWsOffRing + slot * kTileBytes2;
-      if ((tile + 1) * kTN <= kv_hi_all) {            // full tile: no zero-fill predicates
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)sl[i] * stride_b, 16u);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const bool ok = sl[i] >= 0;
-          cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)(ok ? sl[i] : 0) * stride_b, ok ? 16u : 0u);
-        }
-      }
-      cp_async_commit();
-      cp_async_wait<1>();              // everything but the fill just issued has landed
-      fence_proxy_async_smem();
-      if (n == 0) mbar_arrive(bar_q); else mbar_arrive(bar_full((n - 1) % kRing));
-    }
-    cp_async_wait<0>();
-    fence_proxy_async_smem();
-    if (N == 0) mbar_arrive(bar_q); else mbar_arrive(bar_full((N - 1) % kRing));
-  } else if (warp == 8) {
-    // =================================== MMA issuer =======================================================
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    if (J > 0) {   // all 32 lanes run this (warp-uniform); one elected lane issues each tcgen05 op
-      constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
-      constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
-      const uint64_t qdesc0 = make_smem_desc(smem + kWsOffQ, 16, 1024);
-      const uint64_t kdesc0 = make_smem_desc(smem + kWsOffRing, 16, 1024);          // K tiles: K-major
-      const uint64_t vdesc0 = make_smem_desc(smem + kWsOffRing, kBlkBytes, 1024);   // V tiles: MN-major
-      auto issue_qk = [&](int t, int j) {
-        const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
-        const uint64_t kd = kdesc0 + (uint64_t)(((2 * j) % kRing) * (kTileBytes2 >> 4));
-#pragma unroll
-        for (int ks = 0; ks < kTD / 16; ++ks) {
-          const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
-          umma_ss_elect(tmem + t * kTN, qd + koff, kd + koff, idesc_qk, ks > 0);
-        }
-        umma_commit_elect(bar_s(t));
-      };
-      auto issue_pv = [&](int t, int j, int half) {   // half of the 128 tokens of P/V (4 k-steps)
-        const uint64_t vd = vdesc0 + (uint64_t)(((2 * j + 1) % kRing) * (kTileBytes2 >> 4));
-#pragma unroll
-        for (int ks = half * 4; ks < half * 4 + 4; ++ks)
-          umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
-                        (j > 0 || ks > 0));
-      };
-      mbar_wait(bar_q, 0);
-      mbar_wait(bar_full(0), 0);
-      tc_fence_after();
-      if (nt0 > 0) issue_qk(0, 0);
-      if (nt1 > 0) issue_qk(1, 0);
-      umma_commit_elect(bar_empty(0));                                 // K(0) free once both QK(0) are done
-      for (int j = 0; j < J; ++j) {
-        const int nv = 2 * j + 1, nk = 2 * j + 2;
-        mbar_wait(bar_full(nv % kRing), (nv / kRing) & 1);             // V(j)
-        bool k_ready = false;
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          const int ntt = t ? nt1 : nt0;
-          if (j < ntt) {
-            mbar_wait(bar_p(t, 0), j & 1);                             // first 64 columns of P_t(j) are in TMEM
-            tc_fence_after();
-            issue_pv(t, j, 0);
-            mbar_wait(bar_p(t, 1), j & 1);                             // the rest
-            tc_fence_after();
-            issue_pv(t, j, 1);
-            if (j == ntt - 1) umma_commit_elect(bar_o(t));
-          }
-          if (j + 1 < ntt) {
-            if (!k_ready) {
-              mbar_wait(bar_full(nk % kRing), (nk / kRing) & 1);       // K(j+1)
-              tc_fence_after();
-              k_ready = true;
-            }
-            issue_qk(t, j + 1);
-          }
-        }
-        umma_commit_elect(bar_empty(nv % kRing));
-        if (j + 1 < J) umma_commit_elect(bar_empty(nk % kRing));
-      }
-    }
-  } else {
-    // =================================== softmax groups ===================================================
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 200;\n");
-    const int t = warp >> 2;                          // query tile 0/1
-    const int r = tid & 127;                          // row in the tile == TMEM lane
-    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t tS = tmem + lane_base + t * kTN;
-    const uint32_t tO = tmem + lane_base + 2 * kTN + t * kTD;
-    const int my_tok = j0 + t * tok_per_tile + (r >> log2_g);
-    const int lim = p.causal ? (Lkv - Lq + my_tok) : (Lkv - 1);
-    const int lim0 = p.causal ? (Lkv - Lq + j0 + t * tok_per_tile) : (Lkv - 1);
-    const int kv_hi = t ? kvhi1 : kvhi0;
-    const int ntt = t ? nt1 : nt0;
-    const int tokst = t ? toks1 : toks0;
-    float m_used = 0.f, l_run = 0.f;
-    for (int j = 0; j < ntt; ++j) {
-      mbar_wait(bar_s(t), j & 1);
-      tc_fence_after();
-      const int kv0 = j * kTN;
-      const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
-      if (need_mask) {
-        const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
-        softmax_tile<true>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
-      } else {
-        softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
-      }
-    }
-    // ---- epilogue -------------------------------------------------------------------------------------------
-    const bool has = ntt > 0;
-    if (has) {
-      mbar_wait(bar_o(t), 0);
-      tc_fence_after();
-    }
-    const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
-    const bool row_ok = r < (tokst << log2_g);
-    __nv_bfloat16* dst = p.out + (int64_t)(q0 + (row_ok ? my_tok : j0)) * p.out_row_stride + (int64_t)(kvh * G + (r & (G - 1))) * kTD;
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      uint32_t ov[32];
-      if (has) {
-        tmem_ld_32x32b_x32(tO + c * 32, ov);
-        tmem_wait_ld();
-      } else {
-#pragma unroll
-        for (int e = 0; e < 32; ++e) ov[e] = 0u;
-      }
-      if (row_ok) {
-#pragma unroll
-        for (int j8 = 0; j8 < 4; ++j8) {
-          uint4 w;
-          w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
-          w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
-          w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
-          w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
-          *reinterpret_cast<uint4*>(dst + c * 32 + j8 * 8) = w;
-        }
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
-}
 
 // =====================================================================================================
-// Stage 3: the same warp-specialised pipeline made PERSISTENT (the production path).
+// The pipeline is PERSISTENT.
 //
 // One CTA per SM walks a device-built work list instead of paying launch prologue + pipeline ramp
 // per 256-row tile (bench-shaped prompts are 100..1024 tokens: a tile owns only 1..8 KV tiles, so the
@@ -1321,40 +759,13 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   int log2_g = 0;
   while ((1 << log2_g) < p.group) ++log2_g;
   const int tok_per_tile = kTM >> log2_g;
-  // B200ATTN_PREFILL=s1 / ws select the earlier stages (A/B measurements only)
-  static const char mode = [] { const char* e = getenv("B200ATTN_PREFILL"); return e ? e[0] : 'p'; }();
-  if (mode == 's') {   // stage 1: single-tile serial kernel
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaError_t e = cudaFuncSetAttribute(prefill_sm100_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSm100Smem);
-      if (e != cudaSuccess) return fail("b200_prefill(sm100): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      attr_set = true;
-    }
-    const int max_q_tiles = total_q / tok_per_tile + p.B;   // >= sum_i ceil(Lq_i / tok_per_tile)
-    prefill_sm100_kernel<<<dim3(max_q_tiles, p.Hkv), 128, kSm100Smem, st>>>(p, log2_g);
-    return check_launch("b200_prefill(sm100 s1)");
-  }
-  if (mode == 'w') {   // stage 2: warp-specialised, one CTA per 256-row tile
-    static bool attr_ws = false;
-    if (!attr_ws) {
-      cudaError_t e = cudaFuncSetAttribute(prefill_sm100_ws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWsSmem);
-      if (e != cudaSuccess) return fail("b200_prefill(sm100 ws): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      attr_ws = true;
-    }
-    const int max_ctas = total_q / (2 * tok_per_tile) + p.B;
-    prefill_sm100_ws_kernel<<<dim3(max_ctas, p.Hkv), kWsThreads, kWsSmem, st>>>(p, log2_g);
-    return check_launch("b200_prefill(sm100 ws)");
-  }
-  // stage 3 (production): device-built work list + persistent kernel, one CTA per SM
+  // device-built work list + persistent kernel, one CTA per SM
   const size_t need = prefill_sm100_workspace_bytes(p.B, total_q, p.group);
   if (!workspace || workspace_bytes < need) return fail("b200_prefill: workspace %zu < %zu bytes", workspace_bytes, need);
   if ((uintptr_t)workspace & 15) return fail("b200_prefill: workspace must be 16-byte aligned");
-  static bool attr_p = false;
-  if (!attr_p) {
-    cudaError_t e = cudaFuncSetAttribute(prefill_sm100_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kPersistSmem);
-    if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    attr_p = true;
-  }
+  static std::atomic<bool> attr_done[64];
+  if (cudaError_t e = ensure_dyn_smem(prefill_sm100_persist_kernel, kPersistSmem, attr_done); e != cudaSuccess)
+    return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   int* work = reinterpret_cast<int*>(workspace);
   int2* items = reinterpret_cast<int2*>(work + kWorkHeaderInts);
   const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));

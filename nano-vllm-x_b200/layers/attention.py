@@ -85,26 +85,42 @@ class SlotTable:
     """``table[row, pos]`` = KV slot id of token ``pos`` of the live sequence in ``row``.
 
     Workers receive freshly pickled ``Sequence`` objects every step (reference
-    core/executor.py:94-95), so rows are keyed by ``seq_id``.  Contract used for the delta
-    upload: positions ``< seq.cached_kv_len`` were computed in an earlier step and, if this
-    sequence's row already holds at least that many entries, are unchanged; everything from
-    ``min(tracked, cached_kv_len)`` on is (re)sent.  A preempted sequence comes back with
-    ``cached_kv_len == 0`` (core/scheduler.py:130-138) and is therefore resent in full, as is any
-    unknown ``seq_id``.  ``B200ATTN_VERIFY=1`` keeps a host mirror and checks the contract every
-    step (debug aid; O(sum L) like the reference).
+    core/executor.py:94-95), so rows are keyed by ``seq_id``.  Delta contract: a row is trusted only
+    when the sequence continues exactly where this table left it, which is checked in O(1) per
+    sequence from a fingerprint kept on the host:
+
+        tracked == seq.cached_kv_len > 0  and  kv[0] == first slot sent  and  kv[tracked-1] == last slot sent
+
+    Then only ``kv[tracked:]`` (one slot per decode step) is uploaded.  Anything else is resent in
+    full: an unknown ``seq_id``; a preempted sequence (back with ``cached_kv_len == 0``,
+    core/scheduler.py:130-138); a sequence re-admitted with a radix-cache prefix whose slots differ
+    from the ones this row holds (``cached_kv_len = P`` with new prefix slots); a
+    ``seq_id`` reused after its first owner finished (request ids are caller-supplied,
+    entrypoints/openai/serving_completion.py:39).  ``forget(seq_id)`` drops a row explicitly.
+    ``B200ATTN_VERIFY=1`` additionally keeps a full host mirror and checks every step (debug aid;
+    O(sum L) like the reference).
     """
+
+    RING = 4            # pinned staging buffers in flight
 
     def __init__(self, device: torch.device, rows: int = 64, cols: int = 1024):
         self.device = device
         self.table = torch.zeros((rows, cols), dtype=torch.int32, device=device)
         self.row_of: dict = {}
-        self.tracked_len: list[int] = [0] * rows
-        self.last_used: list[int] = [0] * rows
+        self.tracked = np.zeros(rows, dtype=np.int64)
+        self.first = np.full(rows, -1, dtype=np.int64)
+        self.last = np.full(rows, -1, dtype=np.int64)
+        self.last_used = np.zeros(rows, dtype=np.int64)
         self.owner: list = [None] * rows
         self.free_rows = list(range(rows - 1, -1, -1))
         self.step = 0
         self.verify = os.environ.get("B200ATTN_VERIFY", "0") == "1"
         self._mirror: dict = {}
+        self._pin: list = [None] * self.RING
+        self._dev: list = [None] * self.RING
+        self._evt: list = [None] * self.RING
+        self.last_msg_bytes = 0
+        self.full_resends = 0           # sequences uploaded from position 0 (statistics / tests)
 
     # -- capacity ----------------------------------------------------------------------------------
     def _grow(self, rows: int, cols: int) -> None:
@@ -119,84 +135,159 @@ class SlotTable:
         extra = rows - old.shape[0]
         if extra > 0:
             self.free_rows = list(range(rows - 1, old.shape[0] - 1, -1)) + self.free_rows
-            self.tracked_len += [0] * extra
-            self.last_used += [0] * extra
+            self.tracked = np.concatenate([self.tracked, np.zeros(extra, np.int64)])
+            self.first = np.concatenate([self.first, np.full(extra, -1, np.int64)])
+            self.last = np.concatenate([self.last, np.full(extra, -1, np.int64)])
+            self.last_used = np.concatenate([self.last_used, np.zeros(extra, np.int64)])
             self.owner += [None] * extra
 
     def reserve(self, rows: int, cols: int) -> None:
         self._grow(rows, cols)
 
-    def _take_row(self, need_now: int) -> int:
-        if not self.free_rows:
-            # evict rows that are not part of the current step, oldest first
-            stale = [r for r in range(len(self.owner)) if self.last_used[r] != self.step and self.owner[r] is not None]
-            if len(stale) < need_now:
-                self._grow(max(2 * self.table.shape[0], self.table.shape[0] + need_now), self.table.shape[1])
-            else:
-                stale.sort(key=lambda r: self.last_used[r])
-                for r in stale[:max(need_now, len(stale) // 2)]:
-                    self.row_of.pop(self.owner[r], None)
-                    self._mirror.pop(self.owner[r], None)
-                    self.owner[r] = None
-                    self.tracked_len[r] = 0
-                    self.free_rows.append(r)
-        return self.free_rows.pop()
+    def forget(self, seq_id) -> None:
+        """Drop the row of ``seq_id`` (finish / abort / preempt hooks may call this; it is never required
+        for correctness: a stale row fails the fingerprint check and is resent)."""
+        row = self.row_of.pop(seq_id, None)
+        if row is not None:
+            self._mirror.pop(seq_id, None)
+            self.owner[row] = None
+            self.tracked[row] = 0
+            self.first[row] = self.last[row] = -1
+            self.free_rows.append(row)
+
+    def _take_rows(self, need: int) -> None:
+        """Make ``need`` rows available.  Rows of sequences in the current step carry ``last_used == step``
+        (set before any row is taken) and are never evicted."""
+        if len(self.free_rows) >= need:
+            return
+        stale = [r for r in range(len(self.owner)) if self.owner[r] is not None and self.last_used[r] != self.step]
+        if len(stale) + len(self.free_rows) < need:
+            self._grow(max(2 * self.table.shape[0], self.table.shape[0] + need), self.table.shape[1])
+            return
+        stale.sort(key=lambda r: self.last_used[r])
+        for r in stale[:max(need - len(self.free_rows), len(stale) // 2)]:
+            self.forget(self.owner[r])
+
+    # -- staging ------------------------------------------------------------------------------------
+    def _upload(self, msg: np.ndarray) -> torch.Tensor:
+        """One H2D copy of the packed message through a ring of pinned buffers (no allocation per step)."""
+        n = msg.size
+        if self.device.type != "cuda":
+            return torch.from_numpy(msg)
+        i = self.step % self.RING
+        if self._pin[i] is None or self._pin[i].numel() < n:
+            cap = max(4096, 1 << (n - 1).bit_length())
+            self._pin[i] = torch.empty(cap, dtype=torch.int32).pin_memory()
+            self._dev[i] = torch.empty(cap, dtype=torch.int32, device=self.device)
+            self._evt[i] = torch.cuda.Event()
+        else:
+            self._evt[i].synchronize()          # the copy that last used this buffer (RING steps ago) is long done
+        self._pin[i].numpy()[:n] = msg
+        dev = self._dev[i][:n]
+        dev.copy_(self._pin[i][:n], non_blocking=True)
+        self._evt[i].record()
+        return dev
+
+    @staticmethod
+    def _check_pages(seqs, payload, start, cnt, woff, ps: int) -> None:
+        for i in np.flatnonzero(cnt):
+            a, c, st = int(woff[i]), int(cnt[i]), int(start[i])
+            arr = payload[a:a + c].astype(np.int64)
+            pos = st + np.arange(c)
+            head = pos % ps == 0
+            prev = np.empty(c, dtype=np.int64)
+            prev[1:] = arr[:-1]
+            prev[0] = seqs[i].kv_indices[st - 1] if st > 0 else -1
+            if not (np.all(arr[head] % ps == 0) and np.all(arr[~head] == prev[~head] + 1)):
+                raise ValueError(
+                    f"AttentionBackend(page_size={ps}): the KV slots of sequence {seqs[i].seq_id!r} are not "
+                    f"page-aligned runs of {ps} consecutive slots; the reference's token-granular KVCacheAllocator "
+                    "(core/kv_cache.py:101-117) needs page_size=1")
 
     # -- per step ----------------------------------------------------------------------------------
-    def pack_step(self, seqs) -> tuple[torch.Tensor, int, int, int, int]:
-        """Returns (device message, n_payload, total_q, total_pages_at_ps1, total_new)."""
+    def pack_step(self, seqs, page_size: int = 1) -> tuple[torch.Tensor, int, int, int, int]:
+        """Returns (device message, n_payload, total_q, total_kv, total_new).
+
+        ``page_size > 1`` (an extension: the reference is token granular, layers/attention.py:66) needs every
+        page of a sequence to be ``page_size`` consecutive, page-aligned slots; the newly uploaded slots are
+        checked here (O(new) per step) and a violation raises instead of attending the wrong rows.
+
+        Message layout (int32): rows[B] kv_len[B] cached[B] q_len[B] write_col[B] write_cnt[B]
+        write_off[B] payload[n_payload] (include/b200attn.h, b200_slot_table_update)."""
         self.step += 1
-        max_len = 0
-        rows, kvl, cach, qls, wcol, wcnt, woff = [], [], [], [], [], [], []
-        payload: list = []
-        total_q = total_kv = total_new = 0
-        row_of, tracked, last_used, step = self.row_of, self.tracked_len, self.last_used, self.step
-        unknown = -1
-        for s in seqs:
-            kv = s.kv_indices
-            n = len(kv)
-            cached = s.cached_kv_len
-            row = row_of.get(s.seq_id)
-            if row is None:
-                if unknown < 0:
-                    unknown = sum(1 for x in seqs if x.seq_id not in row_of)
-                row = self._take_row(unknown)
-                tracked, last_used = self.tracked_len, self.last_used     # _take_row may have grown them
-                row_of[s.seq_id] = row
-                self.owner[row] = s.seq_id
-                start = 0
-            else:
-                t = tracked[row]
-                start = t if t < cached else cached
-            if self.verify:
+        step = self.step
+        B = len(seqs)
+        row_of = self.row_of
+        rows = np.fromiter((row_of.get(s.seq_id, -1) for s in seqs), dtype=np.int64, count=B)
+        kvl = np.fromiter((len(s.kv_indices) for s in seqs), dtype=np.int64, count=B)
+        cach = np.fromiter((s.cached_kv_len for s in seqs), dtype=np.int64, count=B)
+        ntok = np.fromiter((len(s.token_ids) for s in seqs), dtype=np.int64, count=B)
+        known = rows >= 0
+        self.last_used[rows[known]] = step
+        # O(1) fingerprint per known sequence
+        trusted = known.copy()
+        if known.any():
+            r = np.where(known, rows, 0)
+            t = self.tracked[r]
+            trusted &= (t == cach) & (t > 0) & (kvl >= t)
+            idx = np.flatnonzero(trusted)
+            if idx.size:
+                f0 = np.fromiter((seqs[i].kv_indices[0] for i in idx), dtype=np.int64, count=idx.size)
+                fl = np.fromiter((seqs[i].kv_indices[int(t[i]) - 1] for i in idx), dtype=np.int64, count=idx.size)
+                ok = (f0 == self.first[r[idx]]) & (fl == self.last[r[idx]])
+                trusted[idx[~ok]] = False
+        n_unknown = int(B - known.sum())
+        if n_unknown:
+            self._take_rows(n_unknown)
+            for i in np.flatnonzero(~known):
+                sid = seqs[i].seq_id
+                row = row_of.get(sid)           # the same seq_id twice in one batch shares a row
+                if row is None:
+                    row = self.free_rows.pop()
+                    row_of[sid] = row
+                    self.owner[row] = sid
+                rows[i] = row
+            self.last_used[rows] = step
+        start = np.where(trusted, cach, 0)
+        cnt = np.maximum(kvl - start, 0)
+        woff = np.zeros(B, dtype=np.int64)
+        if B > 1:
+            np.cumsum(cnt[:-1], out=woff[1:])
+        n_payload = int(cnt.sum())
+        payload = np.empty(n_payload, dtype=np.int32)
+        if n_payload == B and bool((cnt == 1).all()):            # steady-state decode: one new slot per sequence
+            payload[:] = np.fromiter((s.kv_indices[-1] for s in seqs), dtype=np.int64, count=B)
+        else:
+            for i in np.flatnonzero(cnt):
+                a, c = int(woff[i]), int(cnt[i])
+                kv = seqs[i].kv_indices
+                payload[a:a + c] = kv if c == len(kv) else kv[len(kv) - c:]
+        self.full_resends += int(((start == 0) & (kvl > 0)).sum())
+        if page_size > 1 and n_payload:
+            self._check_pages(seqs, payload, start, cnt, woff, page_size)
+        if self.verify:
+            for i, s in enumerate(seqs):
                 mir = self._mirror.get(s.seq_id, [])
-                assert mir[:start] == list(kv[:start]), f"slot table contract violated for seq {s.seq_id}"
-                self._mirror[s.seq_id] = list(kv)
-            last_used[row] = step
-            cnt = n - start if n > start else 0
-            q = len(s.token_ids) - cached
-            rows.append(row); kvl.append(n); cach.append(cached); qls.append(q)
-            wcol.append(start); wcnt.append(cnt); woff.append(len(payload))
-            if cnt == 1:
-                payload.append(kv[-1])
-            elif cnt:
-                payload.extend(kv[start:] if start else kv)
-            tracked[row] = n
-            if n > max_len:
-                max_len = n
-            total_q += q
-            total_kv += n
-            if n > cached:
-                total_new += n - cached
+                st = int(start[i])
+                assert mir[:st] == list(s.kv_indices[:st]), f"slot table contract violated for seq {s.seq_id}"
+                self._mirror[s.seq_id] = list(s.kv_indices)
+        # fingerprints for the next step
+        nz = np.flatnonzero(kvl > 0)
+        if nz.size:
+            rr = rows[nz]
+            self.first[rr] = np.fromiter((seqs[i].kv_indices[0] for i in nz), dtype=np.int64, count=nz.size)
+            self.last[rr] = np.fromiter((seqs[i].kv_indices[-1] for i in nz), dtype=np.int64, count=nz.size)
+        self.tracked[rows] = kvl
+        max_len = int(kvl.max()) if B else 0
         if max_len > self.table.shape[1]:      # (the copy of the old contents is ordered before this step's update)
             self._grow(self.table.shape[0], max(max_len, 2 * self.table.shape[1]))
-        msg = np.array(rows + kvl + cach + qls + wcol + wcnt + woff + payload, dtype=np.int32)
-        host = torch.from_numpy(msg)
-        if self.device.type == "cuda":
-            host = host.pin_memory()
-        dev = host.to(self.device, non_blocking=True)
+        qls = ntok - cach
+        msg = np.concatenate([rows, kvl, cach, qls, start, cnt, woff]).astype(np.int32)
+        msg = np.concatenate([msg, payload]) if n_payload else msg
+        dev = self._upload(msg)
         self.last_msg_bytes = msg.nbytes
-        return dev, len(payload), total_q, total_kv, total_new
+        total_new = int(np.maximum(kvl - cach, 0).sum())
+        return dev, n_payload, int(qls.sum()), int(kvl.sum()), total_new
 
 
 # =======================================================================================================
@@ -244,19 +335,20 @@ class AttentionBackend:
         B = len(seqs)
         mode = mode_name(batch.forward_mode)
         st = self.slot_table
-        msg, n_payload, total_q, total_kv, total_new = st.pack_step(seqs)
         ps = self.page_size
+        msg, n_payload, total_q, total_kv, total_new = st.pack_step(seqs, ps)
         if ps == 1:
             n_pages = total_kv
         else:
             n_pages = sum((len(s.kv_indices) + ps - 1) // ps for s in seqs)
         dev = self.device
-        qo_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
-        kv_indptr = torch.empty(B + 1, dtype=torch.int32, device=dev)
-        kv_indices = torch.empty(n_pages, dtype=torch.int32, device=dev)
-        last_page_len = torch.empty(B, dtype=torch.int32, device=dev)
-        out_slots = torch.empty(total_new, dtype=torch.int64, device=dev)
-        scratch = torch.empty(B + 1, dtype=torch.int32, device=dev)
+        # one allocation for the six arrays of a step; every array starts on a 16-byte boundary
+        nb, n64 = (B + 4) & ~3, (2 * total_new + 3) & ~3
+        buf = torch.empty(n64 + 4 * nb + n_pages, dtype=torch.int32, device=dev)
+        out_slots = buf[:2 * total_new].view(torch.int64)
+        qo_indptr, kv_indptr = buf[n64:n64 + B + 1], buf[n64 + nb:n64 + nb + B + 1]
+        scratch, last_page_len = buf[n64 + 2 * nb:n64 + 2 * nb + B + 1], buf[n64 + 3 * nb:n64 + 3 * nb + B]
+        kv_indices = buf[n64 + 4 * nb:n64 + 4 * nb + n_pages]
         if B > 0:
             ops.step_meta(st.table, msg, B, n_payload, B, ps, False, qo_indptr, kv_indptr, kv_indices, last_page_len,
                           out_slots, scratch)
@@ -309,7 +401,7 @@ class AttentionBackend:
         seqs = batch.seqs
         bs = len(seqs)
         st = self.slot_table
-        msg, n_payload, _tq, total_kv, _tn = st.pack_step(seqs)
+        msg, n_payload, _tq, total_kv, _tn = st.pack_step(seqs, self.page_size)
         indptr_buf = graph.get_input_buffer("paged_kv_indptr_buffer")
         indices_buf = graph.get_input_buffer("paged_kv_indices_buffer")
         last_buf = graph.get_input_buffer("paged_kv_last_page_len_buffer")

@@ -71,6 +71,9 @@ PREFILL_CASES = [
     ([150] * 60, [0] * 60, 16, 8, 1),
     ([int(x) for x in np.random.default_rng(5).integers(1, 700, 30)], [int(x) for x in np.random.default_rng(6).integers(0, 300, 30)], 32, 8, 1),
     ([int(x) for x in np.random.default_rng(7).integers(1, 400, 48)], [0] * 48, 4, 1, 16),
+    # GQA groups that do not pack into a 128-row tcgen05 tile: group 3, 5 (Qwen3-14B: 40 / 8 heads) and 6 take the
+    # mma.sync kernel (csrc/prefill_mma.cu), chosen by the shape alone
+    ([70, 200, 5], [0, 33, 64], 6, 2, 1), ([130, 9, 257], [0, 100, 0], 40, 8, 1), ([64, 190], [10, 0], 12, 2, 16),
 ]
 
 
@@ -208,6 +211,69 @@ def test_attention_module_prefill_decode_and_cuda_graph(pkg, Hq, Hkv):
     # padding rows must not have written anything: pools still identical, bit for bit
     assert torch.equal(pool.k_cache.cpu().view(torch.int16), ref_k.view(torch.int16))
     assert torch.equal(pool.v_cache.cpu().view(torch.int16), ref_v.view(torch.int16))
+
+
+def test_readmission_with_remapped_prefix_slots_attends_the_new_slots(pkg, monkeypatch):
+    """Preempt -> re-admit through admission-time prefix reuse: the sequence returns with
+    cached_kv_len = P > 0 and DIFFERENT slots below P while its slot-table row still holds the old ones; then the
+    caller reuses a finished request's seq_id.  B200ATTN_VERIFY is off: the O(1) fingerprint alone must force the
+    resend, otherwise attention silently reads stale rows (layers/attention.py)."""
+    monkeypatch.delenv("B200ATTN_VERIFY", raising=False)
+    Hq, Hkv, D, L, num_slots = 16, 8, 128, 1, 4096
+    devc = torch.device("cuda")
+    pool = pkg.KVCachePool(torch.bfloat16, devc, num_slots, L, Hkv, D)
+    g = torch.Generator().manual_seed(5)
+    pool.k_cache.copy_(torch.randn(pool.k_cache.shape, generator=g).to(torch.bfloat16))
+    pool.v_cache.copy_(torch.randn(pool.v_cache.shape, generator=g).to(torch.bfloat16))
+    ref_k, ref_v = pool.k_cache.cpu().clone(), pool.v_cache.cpu().clone()
+    be = pkg.AttentionBackend(pool, Hq, Hkv, D, torch.bfloat16, devc)
+    assert not be.slot_table.verify
+    model = TinyModel(pkg, Hq, Hkv, D, L).to(devc)
+
+    def step(batch, mode):
+        T = sum(len(s.token_ids) - s.cached_kv_len for s in batch)
+        q, k, v = (torch.randn((T, h * D), generator=g).to(torch.bfloat16) for h in (Hq, Hkv, Hkv))
+        md = be.build_metadata(Batch(mode, batch))
+        with pkg.attention_kv_cache(model, md):
+            out = model.attn[0](q.to(devc), k.to(devc), v.to(devc))
+        ref = _oracle_step(ref_k, ref_v, 0, q, k, v, batch, Hq, Hkv, D)
+        check_close(out.view(-1, Hq, D), ref, f"{mode}")
+
+    a = S("a", [0] * 150, list(range(1000, 1150)), 0)
+    step([a], pkg.ForwardMode.PREFILL)
+    for i in range(2):
+        a.cached_kv_len = len(a.kv_indices); a.token_ids.append(0); a.kv_indices.append(2000 + i)
+        step([a], pkg.ForwardMode.DECODE)
+    # preempted; re-admitted with a 128-token radix hit living in other slots (already holding K/V in the pool)
+    a.kv_indices = list(range(3000, 3128)) + list(range(500, 500 + len(a.token_ids) - 128))
+    a.cached_kv_len = 128
+    resends = be.slot_table.full_resends
+    step([a], pkg.ForwardMode.PREFILL)
+    assert be.slot_table.full_resends == resends + 1
+    a.cached_kv_len = len(a.kv_indices); a.token_ids.append(0); a.kv_indices.append(2100)
+    step([a], pkg.ForwardMode.DECODE)
+    # seq_id reused by a new request whose prefix hit happens to be as long as the old tracked length
+    n_old = len(a.kv_indices)
+    b = S("a", [0] * (n_old + 1), list(range(3500, 3500 + n_old)) + [2200], n_old)
+    step([b], pkg.ForwardMode.PREFILL)
+
+
+def test_page_size_16_rejects_token_granular_slots(pkg):
+    """page_size > 1 needs page-aligned runs of consecutive slots (csrc/meta.cu): the reference's
+    token-granular allocator hands out arbitrary slots, which must raise instead of attending the wrong rows."""
+    devc = torch.device("cuda")
+    pool = pkg.KVCachePool(torch.bfloat16, devc, 1024, 1, 2, 128)
+    be = pkg.AttentionBackend(pool, 8, 2, 128, torch.bfloat16, devc, page_size=16)
+    ok = S("ok", [0] * 40, list(range(64, 96)) + list(range(16, 24)), 0)
+    be.build_metadata(Batch(pkg.ForwardMode.PREFILL, [ok]))
+    ok.cached_kv_len = 40; ok.token_ids.append(0); ok.kv_indices.append(24)
+    be.build_metadata(Batch(pkg.ForwardMode.DECODE, [ok]))
+    bad = S("bad", [0] * 20, [int(x) for x in np.random.default_rng(0).permutation(512)[:20]], 0)
+    with pytest.raises(ValueError):
+        be.build_metadata(Batch(pkg.ForwardMode.PREFILL, [bad]))
+    ok.cached_kv_len = 41; ok.token_ids.append(0); ok.kv_indices.append(300)      # breaks the run inside a page
+    with pytest.raises(ValueError):
+        be.build_metadata(Batch(pkg.ForwardMode.DECODE, [ok]))
 
 
 # ---- size-independent properties at (near) full size ------------------------------------------------

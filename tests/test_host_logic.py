@@ -72,14 +72,96 @@ def test_delta_protocol_prefill_decode_preempt(pkg):
     step(many[:20] + [seqs[2]])
 
 
-def test_verify_mode_detects_contract_violation(pkg, monkeypatch):
+def _check(st, batch):
+    """pack_step -> modelled kernels -> arrays equal to the oracle's for this batch; returns n_payload."""
+    msg, n_pay, tq, tkv, tnew = st.pack_step(batch)
+    table_now = st.table.numpy()
+    apply_update(table_now, msg.numpy(), len(batch), n_pay)
+    md = model_build_meta(table_now, msg.numpy(), len(batch), 1)
+    ref = orc.build_metadata([orc.SeqView(len(s.token_ids), s.kv_indices, s.cached_kv_len) for s in batch])
+    for f in ("qo_indptr", "paged_kv_indptr", "paged_kv_indices", "paged_kv_last_page_len", "output_kv_indices"):
+        np.testing.assert_array_equal(getattr(md, f), getattr(ref, f))
+    return n_pay
+
+
+def test_preempt_then_readmit_with_a_radix_prefix_of_different_slots(pkg, monkeypatch):
+    """SURVEY.md 8 f-1 + core/scheduler.py:130-153: a preempted sequence comes back through admission-time prefix
+    reuse with cached_kv_len = P > 0 and DIFFERENT slots below P while its row still tracks the old length.  The
+    O(1) fingerprint must turn that into a full resend (B200ATTN_VERIFY off: no host mirror involved)."""
+    monkeypatch.delenv("B200ATTN_VERIFY", raising=False)
+    st = pkg.SlotTable(torch.device("cpu"), rows=4, cols=64)
+    a = S("a", 20, range(100, 120), 0)
+    assert _check(st, [a]) == 20
+    for _ in range(2):
+        a.cached_kv_len = len(a.kv_indices); a.token_ids.append(0); a.kv_indices.append(500 + len(a.kv_indices))
+        assert _check(st, [a]) == 1
+    # preempted (slots freed), re-admitted: 16-token prefix served by the radix tree from OTHER slots
+    a.kv_indices = list(range(900, 916)) + list(range(300, 300 + len(a.token_ids) - 16))
+    a.cached_kv_len = 16
+    before = st.full_resends
+    assert _check(st, [a]) == len(a.kv_indices)
+    assert st.full_resends == before + 1
+    # the same with a prefix exactly as long as the tracked length (only the fingerprint can tell)
+    b = S("b", 8, range(40, 48), 0)
+    assert _check(st, [b]) == 8
+    b.kv_indices = list(range(700, 708)) + [55]
+    b.cached_kv_len = 8
+    b.token_ids.append(0)
+    assert _check(st, [b]) == 9
+    # ... and when only the END of the cached part moved (first slot unchanged)
+    c = S("c", 8, range(60, 68), 0)
+    assert _check(st, [c]) == 8
+    c.kv_indices = list(range(60, 64)) + list(range(800, 804)) + [56]
+    c.cached_kv_len = 8
+    c.token_ids.append(0)
+    assert _check(st, [c]) == 9
+
+
+def test_seq_id_reused_after_finish_and_forget(pkg):
+    st = pkg.SlotTable(torch.device("cpu"), rows=4, cols=64)
+    a = S("req-1", 6, range(10, 16), 0)
+    assert _check(st, [a]) == 6
+    a.cached_kv_len = 6; a.token_ids.append(0); a.kv_indices.append(99)
+    assert _check(st, [a]) == 1
+    # the caller reuses the id for a new request (serving_completion.py:39): new slots, nothing cached
+    a2 = S("req-1", 9, range(200, 209), 0)
+    assert _check(st, [a2]) == 9
+    # explicit forget: the row goes back to the free list and the next step re-uploads
+    rows_free = len(st.free_rows)
+    st.forget("req-1")
+    assert len(st.free_rows) == rows_free + 1 and "req-1" not in st.row_of
+    a2.cached_kv_len = 9; a2.token_ids.append(0); a2.kv_indices.append(98)
+    assert _check(st, [a2]) == 10
+    st.forget("never-seen")
+
+
+def test_rows_of_the_current_batch_are_never_evicted(pkg):
+    """Two rows, both owned by sequences of this step, plus newcomers: the table must grow, not recycle rows of
+    sequences that the packing loop has not reached yet."""
+    st = pkg.SlotTable(torch.device("cpu"), rows=2, cols=16)
+    a, b = S("a", 3, [1, 2, 3], 0), S("b", 3, [4, 5, 6], 0)
+    assert _check(st, [a, b]) == 6
+    for s, slot in ((a, 7), (b, 8)):
+        s.cached_kv_len = 3; s.token_ids.append(0); s.kv_indices.append(slot)
+    c, d = S("c", 2, [9, 10], 0), S("d", 2, [11, 12], 0)
+    before = st.full_resends
+    assert _check(st, [c, a, d, b]) == 2 + 1 + 2 + 1
+    assert st.full_resends == before + 2          # only the newcomers
+    assert st.table.shape[0] >= 4
+
+
+def test_verify_mode_detects_what_the_fingerprint_cannot(pkg, monkeypatch):
     import pytest
     monkeypatch.setenv("B200ATTN_VERIFY", "1")
     st = pkg.SlotTable(torch.device("cpu"))
     s = S("a", 4, [1, 2, 3, 4], 0)
     st.pack_step([s])
-    s.kv_indices = [9, 2, 3, 4, 5]   # prefix rewritten in place while cached_kv_len says it is old
+    s.kv_indices = [9, 2, 3, 4, 5]   # first slot rewritten: the fingerprint sees it and resends in full
     s.cached_kv_len = 4
+    s.token_ids.append(0)
+    assert st.pack_step([s])[1] == 5
+    s.kv_indices = [9, 2, 77, 4, 5, 6]   # a slot strictly inside the cached part: only the host mirror can tell
+    s.cached_kv_len = 5
     s.token_ids.append(0)
     with pytest.raises(AssertionError):
         st.pack_step([s])
