@@ -207,6 +207,12 @@ def apply_patches(cfg: dict) -> None:
         # An environment bug in a component outside the path: Sampler.forward runs eagerly, in EVERY arm.
         import nanovllmx.layers.sampler as SM
         SM.Sampler.forward = getattr(SM.Sampler.forward, "_torchdynamo_orig_callable", SM.Sampler.forward)
+    if cfg.get("argmax"):
+        # Token-identity experiments only: plain argmax in EVERY arm.  The reference's deterministic form (top_k=1,
+        # layers/sampler.py:68-74) keeps all logits tied with the maximum and lets torch.multinomial pick among them,
+        # so exact bf16 ties (frequent on random-init weights) make even two runs of one arm differ.
+        import nanovllmx.layers.sampler as SM
+        SM.Sampler.forward = lambda self, logits, *a, **k: logits.argmax(dim=-1)
     if not cfg.get("verbose"):
         E.print = lambda *a, **k: None          # "Added sequence <id>" x 256 (core/engine.py:70)
     if cfg["backend"] == "b200":
@@ -265,7 +271,7 @@ async def run(cfg: dict) -> dict:
     tp = cfg["tp"]
     t_init = time.time()
     llm = LLM(model=cfg["model_dir"], gpu_memory_utilization=0.8, max_bs=cfg["max_bs"], tp_size=tp, pp_size=1,
-              nccl_port=cfg["nccl_port"], device_ids=None if cfg["backend"] == "oracle" else list(range(tp)),
+              nccl_port=cfg["nccl_port"], device_ids=None if cfg["backend"] == "oracle" else (cfg.get("device_ids") or list(range(tp))),
               enforce_eager=cfg["enforce_eager"], context_len=cfg["context_len"])
 
     def params(i):
@@ -284,7 +290,7 @@ async def run(cfg: dict) -> dict:
     await _consume(llm.generate("Benchmark: ", SamplingParams(max_tokens=10)), warm)       # bench.py:31
     init_s = time.time() - t_init
     runs = []
-    tokens = None
+    tokens_runs = []
     for r in range(cfg["runs"]):
         sinks = [[] for _ in prompts]
         t = time.time()
@@ -294,10 +300,10 @@ async def run(cfg: dict) -> dict:
         ref_total = sum(max_tokens) if max_tokens is not None else gen
         runs.append(dict(wall_s=t, tok_s_reference_formula=ref_total / t, tok_s_generated=gen / t, generated=gen,
                          reference_formula_tokens=ref_total))
-        if tokens is None:
-            tokens = sinks
+        tokens_runs.append(sinks)
     llm.shutdown()
-    return dict(init_s=init_s, runs=runs, tokens=tokens, prompt_tokens=sum(len(p) for p in prompts))
+    return dict(init_s=init_s, runs=runs, tokens=tokens_runs[0], tokens_runs=tokens_runs,
+                prompt_tokens=sum(len(p) for p in prompts))
 
 
 def main():
@@ -311,7 +317,8 @@ def main():
     ap.add_argument("--workload", default="bench", choices=["bench", "shared-prefix"])
     ap.add_argument("--runs", type=int, default=2, help="timed passes over the workload; the first follows the "
                     "reference bench.py protocol (only a 1-request warm-up before it), later ones are steady state")
-    ap.add_argument("--greedy", action="store_true")
+    ap.add_argument("--greedy", action="store_true", help="top_k=1, temperature 1: the reference's deterministic form")
+    ap.add_argument("--argmax", action="store_true", help="token-identity experiments: plain argmax sampler in every arm")
     ap.add_argument("--enforce-eager", action="store_true")
     ap.add_argument("--fused-qk", action="store_true")
     ap.add_argument("--b200-sampler", action="store_true")
@@ -320,6 +327,7 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--init-std", type=float, default=0.02)
     ap.add_argument("--nccl-port", type=int, default=29511)
+    ap.add_argument("--device-ids", default=None, help="comma-separated physical GPU ids (default 0..tp-1)")
     ap.add_argument("--stats", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--out", default=None)
@@ -327,10 +335,10 @@ def main():
     if not os.path.isdir(os.path.join(REF_DIR, "nanovllmx", "core")):
         raise SystemExit(f"{REF_DIR} is missing or incomplete: run `python baseline/install_ref.py` in the build container")
     cfg = dict(model=a.model, model_dir=write_model_dir(a.model), backend=a.backend, tp=a.tp, num_seqs=a.num_seqs,
-               max_bs=a.max_bs, context_len=a.context_len, workload=a.workload, runs=a.runs, greedy=a.greedy,
+               max_bs=a.max_bs, context_len=a.context_len, workload=a.workload, runs=a.runs, greedy=a.greedy or a.argmax, argmax=a.argmax,
                enforce_eager=a.enforce_eager or a.backend == "oracle", fused_qk=a.fused_qk, b200_sampler=a.b200_sampler,
                prefix_cache=a.prefix_cache, wire=a.wire, seed=a.seed, init_std=a.init_std, nccl_port=a.nccl_port,
-               verbose=a.verbose)
+               verbose=a.verbose, device_ids=[int(x) for x in a.device_ids.split(",")] if a.device_ids else None)
     if a.stats:
         cfg["stats_path"] = (a.out or "/tmp/ref_engine") + ".steps.json"
     os.environ[CFG_ENV] = json.dumps(cfg)
@@ -351,7 +359,7 @@ def main():
     print("REF_ENGINE_RESULT " + json.dumps(summary))
     if a.out:
         with open(a.out, "w") as f:
-            json.dump(dict(summary, tokens=res["tokens"]), f)
+            json.dump(dict(summary, tokens=res["tokens"], tokens_runs=res["tokens_runs"]), f)
 
 
 if __name__ == "__main__":

@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 O=gpurun_out
 nvidia-smi --query-gpu=name,memory.total --format=csv > $O/r2s1_smi.txt 2>&1
 nproc >> $O/r2s1_smi.txt
-timeout 900 python -m pytest tests -m gpu -x -q --deselect tests/test_gpu_ref_engine.py > $O/r2s1_pytest_base.log 2>&1
+timeout 900 python -m pytest tests -m gpu -x -q --deselect tests/test_zz_gpu_ref_engine.py > $O/r2s1_pytest_base.log 2>&1
 echo "pytest_base rc=$?" >> $O/r2s1_status.txt
 for arm in stock b200; do
   timeout 900 python benchmarks/ref_engine.py --model 0.6b --backend $arm --greedy --runs 2 --stats --out $O/r2s1_eng06_${arm}_greedy.json > $O/r2s1_eng06_${arm}_greedy.log 2>&1

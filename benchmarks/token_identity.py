@@ -14,7 +14,7 @@ statement checkable instead of eyeballed.  For every sequence whose token lists 
 
 and records, from the last position's logits: the two tokens the arms picked, their fp32-flavour logit difference
 (the "margin" that decided the flip), the bf16 ulp at that logit magnitude, and max |logits - logits_fp32| for fi
-and b200.  tests/test_gpu_ref_engine.py asserts on the report: every divergence is decided by a margin of at most
+and b200.  tests/test_zz_gpu_ref_engine.py asserts on the report: every divergence is decided by a margin of at most
 MARGIN_ULPS bf16 ulps, and b200's logit error against fp32 is not larger than FlashInfer's beyond noise.
 
   python benchmarks/token_identity.py --stock a.json --b200 b.json --out report.json
@@ -73,7 +73,7 @@ class _Fp32Wrapper:
         s = torch.matmul(Q, K.transpose(1, 2)) * self._sm_scale
         s = s.masked_fill(torch.ones(T, T, dtype=torch.bool, device=q.device).triu(1), float("-inf"))
         o = torch.matmul(torch.softmax(s, dim=-1), V)
-        return o.transpose(0, 1).to(q.dtype)
+        return o.transpose(0, 1).contiguous().to(q.dtype)
 
 
 def arbitrate(cfg, prompts, tok_stock, tok_b200, max_cases=None):

@@ -1,9 +1,10 @@
 """GPU: the drop-in, dropped in.  The STOCK reference engine (baseline/_ref: LLM -> Engine -> Scheduler/RadixTree ->
 Executor -> Worker -> ModelRunner with CUDA-graph capture at start-up and graph replay for every decode step,
 core/model_runner.py:133-157, 276-330, 332-417) runs the reference's bench.py request generator twice: as shipped
-(FlashInfer + Triton) and with INTEGRATION.md section 1's monkey-patch.  Greedy (top_k=1, the reference's only
-deterministic mode) tokens are compared; every divergence is arbitrated against an fp32-attention forward of the
-same model on the same prefix (benchmarks/token_identity.py)."""
+(FlashInfer + Triton) and with INTEGRATION.md section 1's monkey-patch.  Greedy tokens (plain argmax in both arms: the reference's top_k=1 form
+breaks exact bf16 ties with torch.multinomial, which makes even two runs of ONE arm differ) are compared; every
+divergence is arbitrated against an fp32-attention forward of the same model on the same prefix
+(benchmarks/token_identity.py)."""
 import json
 import os
 import subprocess
@@ -33,7 +34,7 @@ def engine_runs():
     for arm, port in (("stock", 29531), ("b200", 29541)):
         paths[arm] = os.path.join(OUT, f"test_ref_engine_{arm}.json")
         _run(["benchmarks/ref_engine.py", "--model", "0.6b", "--backend", arm, "--num-seqs", str(NUM_SEQS), "--max-bs", "32",
-              "--greedy", "--runs", "1", "--nccl-port", str(port), "--out", paths[arm]], timeout=900)
+              "--argmax", "--runs", "1", "--nccl-port", str(port), "--out", paths[arm]], timeout=900)
     return paths
 
 
