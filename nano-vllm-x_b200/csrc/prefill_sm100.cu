@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "prefill_params.cuh"
 #include "sm100.cuh"
+#include "tma.cuh"
 
 namespace b200 {
 
@@ -48,7 +49,6 @@ constexpr int kTileBytes2 = 2 * kBlkBytes;     // a full [128 x 128] bf16 operan
 // (exact: O and l carry the same stale scale until the final division).
 // =====================================================================================================
 constexpr int kWsThreads = 384;   // 3 warpgroups: softmax0, softmax1, {MMA, 2 loaders, 1 spare}
-constexpr int kWsLoaders = 64;
 constexpr int kRing = 4;
 constexpr int kWsOffQ = 0;                           // 2 x 32 KiB
 constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
@@ -279,12 +279,12 @@ __global__ void __launch_bounds__(kPlanThreads, 1) prefill_plan_kernel(const Pre
 __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(const PrefillParams p, const int log2_g,
                                                                                int* __restrict__ work,
                                                                                const int2* __restrict__ items,
-                                                                               const int flags) {
-  (void)flags;
+                                                                               const __grid_constant__ CUtensorMap tm_q,
+                                                                               const __grid_constant__ CUtensorMap tm_k,
+                                                                               const __grid_constant__ CUtensorMap tm_v) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem;
   __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing];
-  __shared__ __align__(16) int s_slots[2][2][2][32];   // [tile parity][loader warp][row parity][i]
   __shared__ __align__(16) ItemDesc s_items[kItemRing];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -313,13 +313,13 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   auto bar_o = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 6 + t); };
   auto bar_ifull = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + slot); };
   auto bar_iempty = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + kItemRing + slot); };
-  constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 loader warps (lane 0 of each arrives)
+  constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 TMA warps (lane 0 of each arrives)
 
   if (tid == 0) {
-    mbar_init(bar_q, kWsLoaders);
+    mbar_init(bar_q, 1);              // one arrive.expect_tx by the TMA warp + the transaction bytes
     mbar_init(bar_qfree, 1);
     for (int i = 0; i < kRing; ++i) {
-      mbar_init(bar_full(i), kWsLoaders);
+      mbar_init(bar_full(i), 1);
       mbar_init(bar_empty(i), 1);
     }
     for (int t = 0; t < 2; ++t) {
@@ -386,159 +386,68 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       if (!valid) break;
     }
   } else if (warp >= 9) {
-    // =================================== loaders ==========================================================
+    // =================================== TMA producers =====================================================
+    // Warp 9 stages Q and the K tiles, warp 10 the V tiles (ring slots alternate K0 V0 K1 V1 ...).
+    // Q: four tiled 3-D boxes per item ([64 d] x [G heads] x [128/G tokens]: two query tiles x two 64-column halves;
+    // rows past the sequence / past T are other tokens or zero fill and their outputs are never stored).
+    // K/V: tile::gather4 through the page table -- lane l owns tile rows 4l..4l+3, so a 128-token tile is 2
+    // instructions per lane (one per 64-column half): 64 TMA instructions per tile instead of 2048 LDGSTS.  ptxas
+    // issues a per-lane instruction with lane-varying operands as a 32-trip elect loop (~14 instructions per trip),
+    // which is why K and V have a warp each.  Rows past the end of the sequence re-read its last valid slot
+    // (finite data; their S columns are masked to -inf, their P is exactly 0).  Completion is counted in bytes on
+    // the ring's mbarriers (arrive.expect_tx).
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    const int lt = tid - 9 * 32;                    // 0..63
-    const int gc = lt & 15, lrow0 = lt >> 4;        // rows lrow0 + 4*i
-    const uint32_t chunk_off = (uint32_t)(gc >> 3) * kBlkBytes;
-    const int c8 = gc & 7;
     const int ps_mask = (1 << p.log2_ps) - 1;
-    const int lw = warp - 9;
-    const int hrow = lane >> 4;
-    const uint32_t stride_b = (uint32_t)(p.kv_slot_stride * 2);   // bytes between token slots (< 4 GiB)
-    const uint32_t dst_even = chunk_off + lrow0 * 128 + ((c8 ^ lrow0) << 4);
-    const uint32_t dst_odd = chunk_off + lrow0 * 128 + ((c8 ^ (lrow0 + 4)) << 4);
-    // One cp.async group per fill (Q, K(0), V(0), K(1), ...).  A fill's mbarrier is signalled when the NEXT
-    // fill has been issued (wait_group 1), so one fill is always in flight; before blocking on anything
-    // that may depend on the consumers, the pending fill is flushed.
-    uint32_t pend_bar = 0;
-    auto rotate = [&](uint32_t this_bar) {
-      cp_async_commit();
-      cp_async_wait<1>();
-      fence_proxy_async_smem();
-      if (pend_bar) mbar_arrive(pend_bar);
-      pend_bar = this_bar;
-    };
-    auto flush = [&]() {
-      cp_async_wait<0>();
-      fence_proxy_async_smem();
-      if (pend_bar) mbar_arrive(pend_bar);
-      pend_bar = 0;
-    };
-    auto wait_or_flush = [&](uint32_t bar, uint32_t parity) {
-      if (!mbar_test_wait(bar, parity)) {
-        flush();
-        mbar_wait(bar, parity);
-      }
-    };
-    int fill = 0, qn = 0;
-    int sl[32];
+    const int is_v = warp - 9;                       // 0: Q + K tiles, 1: V tiles
+    const CUtensorMap* tm = is_v ? &tm_v : &tm_k;
+    if (lane == 0) {
+      tma::prefetch_desc(tm);
+      if (!is_v) tma::prefetch_desc(&tm_q);
+    }
+    int fill = is_v, qn = 0;                         // running ring-fill index of this warp's next tile
     for (int it = 0;; ++it) {
-      {
-        const int islot = it % kItemRing;
-        wait_or_flush(bar_ifull(islot), (it / kItemRing) & 1);
-      }
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
       const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
       if (g.J == 0) continue;
-      const int kvh = d.kvh;
       const uint32_t smem_q = smem + kWsOffQ, smem_ring = smem + kWsOffRing;
-      // ---- Q: 256 packed rows ------------------------------------------------------------------------------
-      // Page ids of KV tile 0: issued here, consumed (slot arithmetic + smem store) only after the Q fill, so the
-      // load latency hides behind the 64 cp.async of Q instead of stalling the warp (the blocking form cost the
-      // loaders 25 % of their time on bench-shaped prompts: ncu source page, long-scoreboard stalls).
-      int pg_a = -1, pg_b = -1;
-      auto ldg_pages = [&](int tile) {
-        const int tok = tile * kTN + 4 * lane + 2 * lw;
-        pg_a = pg_b = -1;
-        if (tok < g.kv_hi_all) pg_a = __ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps));
-        if (tok + 1 < g.kv_hi_all) pg_b = __ldg(p.kv_indices + d.page0 + ((tok + 1) >> p.log2_ps));
-      };
-      auto put_slots = [&](int tile) {
-        const int tok = tile * kTN + 4 * lane + 2 * lw;
-        s_slots[tile & 1][lw][0][lane] = pg_a >= 0 ? (pg_a << p.log2_ps) + (tok & ps_mask) : -1;
-        s_slots[tile & 1][lw][1][lane] = pg_b >= 0 ? (pg_b << p.log2_ps) + ((tok + 1) & ps_mask) : -1;
-      };
-      ldg_pages(0);
-      wait_or_flush(bar_qfree, (qn & 1) ^ 1);
-      {
-        // 256 packed rows; this thread owns rows lrow0 + 4 i.  Row R -> (token j0 + R / G, head kvh G + R % G).
-        const int rows_total = (g.toks0 + g.toks1) << log2_g;
-        if (lean_q && p.q_row_stride > 0 && p.q_row_stride < (1 << 22)) {
-          // lean form (32-bit offsets from the item's first row, ~8 instructions per cp.async; the general form
-          // below costs 29 and made the Q fill 60 % of all loader instructions on bench-shaped prompts)
-          const char* qbase = reinterpret_cast<const char*>(p.q + (int64_t)(d.q0 + d.j0) * p.q_row_stride +
-                                                            (int64_t)kvh * G * kTD + gc * 8);
-          const uint32_t stride_q = (uint32_t)p.q_row_stride * 2u, gmask = (uint32_t)G - 1u;
-          if (rows_total == 2 * kTM) {
-#pragma unroll 1
-            for (int io = 0; io < 64; io += 8) {
-              const uint32_t dbase = smem_q + io * 512 + (io >= 32 ? 16384 : 0);
+      const int last_tok = g.kv_hi_all - 1;
+      const int last_slot = (__ldg(p.kv_indices + d.page0 + (last_tok >> p.log2_ps)) << p.log2_ps) + (last_tok & ps_mask);
+      int sl[4], sn[4];
+      auto ldg_slots = [&](int tile, int (&dst)[4]) {
 #pragma unroll
-              for (int u = 0; u < 8; ++u) {
-                const uint32_t R = (uint32_t)lrow0 + 4u * (io + u);
-                const uint32_t off = (R >> log2_g) * stride_q + (R & gmask) * (kTD * 2);
-                cp_async_16(dbase + ((u & 1) ? dst_odd : dst_even) + u * 512, qbase + off, 16u);
-              }
-            }
-          } else {
-#pragma unroll 1
-            for (int io = 0; io < 64; io += 8) {
-              const uint32_t dbase = smem_q + io * 512 + (io >= 32 ? 16384 : 0);
-#pragma unroll
-              for (int u = 0; u < 8; ++u) {
-                const uint32_t R = (uint32_t)lrow0 + 4u * (io + u);
-                const bool ok = R < (uint32_t)rows_total;
-                const uint32_t off = ok ? (R >> log2_g) * stride_q + (R & gmask) * (kTD * 2) : 0u;
-                cp_async_16(dbase + ((u & 1) ? dst_odd : dst_even) + u * 512, qbase + off, ok ? 16u : 0u);
-              }
-            }
-          }
-        } else {
-#pragma unroll 4
-          for (int i = 0; i < 256 / 4; ++i) {
-            const int R = lrow0 + 4 * i;                  // packed row 0..255
-            const bool ok = R < rows_total;
-            const int tok = d.j0 + (R >> log2_g), head = kvh * G + (R & (G - 1));
-            const __nv_bfloat16* src = p.q + (int64_t)(d.q0 + (ok ? tok : d.j0)) * p.q_row_stride +
-                                       (int64_t)(ok ? head : kvh * G) * kTD + gc * 8;
-            const int r = R & 127;
-            cp_async_16(smem_q + (R >> 7) * kTileBytes2 + chunk_off + r * 128 + ((c8 ^ (r & 7)) << 4), src,
-                        ok ? 16u : 0u);
-          }
+        for (int i = 0; i < 4; ++i) {
+          const int tok = tile * kTN + 4 * lane + i;
+          dst[i] = tok <= last_tok ? (__ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps)) << p.log2_ps) + (tok & ps_mask) : last_slot;
         }
+      };
+      ldg_slots(0, sl);
+      // ---- Q: 256 packed rows; row R of tile t = (token j0 + t*tok_per_tile + R / G, head kvh*G + R % G) ---------
+      if (!is_v && lane == 0) {
+        mbar_wait(bar_qfree, (qn & 1) ^ 1);
+        tma::mbar_expect_tx(bar_q, 2 * kTileBytes2);
+#pragma unroll
+        for (int t = 0; t < 2; ++t)
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            tma::load_3d(smem_q + t * kTileBytes2 + h * kBlkBytes, &tm_q, bar_q, h * 64, d.kvh * G, d.q0 + d.j0 + t * tok_per_tile);
       }
-      rotate(bar_q);
       ++qn;
-      put_slots(0);
-      const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)kvh * kTD + gc * 8);
-      const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)kvh * kTD + gc * 8);
-      const int N = 2 * g.J;
-      for (int n = 0; n < N; ++n, ++fill) {
+      const int col = d.kvh * kTD;
+      for (int tile = 0; tile < g.J; ++tile, fill += 2) {
         const int slot = fill % kRing, use = fill / kRing;
-        const int tile = n >> 1;
-        if ((n & 1) == 0) {
-          __syncwarp();
-          const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
+        if (tile + 1 < g.J) ldg_slots(tile + 1, sn);      // in flight behind this tile's issue loop
+        mbar_wait(bar_empty(slot), (use & 1) ^ 1);
+        const uint32_t full = bar_full(slot);
+        if (lane == 0) tma::mbar_expect_tx(full, kTileBytes2);
+        __syncwarp();
+        const uint32_t dst = smem_ring + slot * kTileBytes2 + lane * 512;
+        tma::gather4(dst, tm, full, col, sl[0], sl[1], sl[2], sl[3]);
+        tma::gather4(dst + kBlkBytes, tm, full, col + 64, sl[0], sl[1], sl[2], sl[3]);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int4 v = src[i];
-            sl[4 * i] = v.x; sl[4 * i + 1] = v.y; sl[4 * i + 2] = v.z; sl[4 * i + 3] = v.w;
-          }
-          __syncwarp();
-          if (tile + 1 < g.J) ldg_pages(tile + 1);          // consumed after the V fill of this tile
-        }
-        wait_or_flush(bar_empty(slot), (use & 1) ^ 1);
-        const char* base = (n & 1) ? vbase : kbase;
-        const uint32_t dst0 = smem_ring + slot * kTileBytes2;
-        if ((tile + 1) * kTN <= g.kv_hi_all) {            // full tile: no zero-fill predicates
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)sl[i] * stride_b, 16u);
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const bool ok = sl[i] >= 0;
-            cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)(ok ? sl[i] : 0) * stride_b,
-                        ok ? 16u : 0u);
-          }
-        }
-        rotate(bar_full(slot));
-        if ((n & 1) && tile + 1 < g.J) put_slots(tile + 1);
+        for (int i = 0; i < 4; ++i) sl[i] = sn[i];
       }
     }
-    flush();
   } else if (warp == 8) {
     // =================================== MMA issuer =======================================================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
@@ -771,9 +680,28 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
   prefill_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, 2 * tok_per_tile, work, items, max_pairs);
   if (int rc = check_launch("b200_prefill(plan)")) return rc;
-  const int flags = 0;  // reserved
+  // Tensor maps (host-encoded per call: q and the layer's pool pointers change between calls; the maps travel as
+  // __grid_constant__ kernel parameters, so the launch stays CUDA-graph capturable).
+  //   Q  : [T tokens][Hq heads][128 d], box [tok_per_tile][G][64]  -> one box = one 64-column half of a 128-row packed tile
+  //   K/V: [slots][Hkv * 128], box [1][64], issued as tile::gather4 (four token slots per instruction).  The pool's
+  //        slot count is not part of the C ABI; the extent is an upper bound (rows are only touched through valid slot
+  //        ids, and out-of-range tile rows re-read a valid slot, so no out-of-bounds fill is relied on).
+  CUtensorMap tm_q, tm_k, tm_v;
+  {
+    const int G = 1 << log2_g;
+    const uint64_t qd[3] = {(uint64_t)kTD, (uint64_t)p.Hq, (uint64_t)total_q};
+    const uint64_t qs[2] = {(uint64_t)kTD * 2, (uint64_t)p.q_row_stride * 2};
+    const uint32_t qb[3] = {64u, (uint32_t)G, (uint32_t)tok_per_tile};
+    const uint64_t kd[2] = {(uint64_t)p.Hkv * kTD, (uint64_t)1 << 30};
+    const uint64_t ks[1] = {(uint64_t)p.kv_slot_stride * 2};
+    const uint32_t kb[2] = {64u, 1u};
+    if (!tma::encode_bf16(&tm_q, p.q, 3, qd, qs, qb) || !tma::encode_bf16(&tm_k, p.k_cache, 2, kd, ks, kb) ||
+        !tma::encode_bf16(&tm_v, p.v_cache, 2, kd, ks, kb))
+      return fail("b200_prefill: cuTensorMapEncodeTiled failed (q stride %lld, kv slot stride %lld)", (long long)p.q_row_stride,
+                  (long long)p.kv_slot_stride);
+  }
   cudaError_t e = launch_pdl(prefill_sm100_persist_kernel, dim3(cached_num_sms()), dim3(kWsThreads), kPersistSmem, st, p, log2_g, work,
-                             (const int2*)items, flags);
+                             (const int2*)items, tm_q, tm_k, tm_v);
   if (e != cudaSuccess) return fail("b200_prefill(sm100 persist): %s", cudaGetErrorString(e));
   return check_launch("b200_prefill(sm100 persist)");
 }
