@@ -593,6 +593,8 @@ def run_b200_arm(args):
     except Exception:
         pass
 
+    timed_region = "eager launches" if graph is None else "CUDA-graph replays of the step (as the reference replays decode)"
+
     # ---- (D) extra keys: prefill roofline, FlashInfer on the same inputs, the stock engine ---------------------
     prefill = gpu_ref = engine = None
     if rank == 0 and not args.no_prefill:
@@ -617,8 +619,7 @@ def run_b200_arm(args):
         # every rank lets go of its device memory; rank 0 runs the engine (its own processes, tp = N) while the others
         # wait on the host
         del pool, k_cache, v_cache, ws, big
-        if graph is not None:
-            del graph, gdec
+        graph = gdec = None
         import gc
         gc.collect()
         torch.cuda.empty_cache()
@@ -643,7 +644,7 @@ def run_b200_arm(args):
                          "read_only_stream_gbs_live": read_only_gbs, "frac_of_read_only_stream": achieved / read_only_gbs},
             "prefill": prefill, "gpu_reference": gpu_ref, "engine": engine,
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
-            "timing": {"timed_region": "eager launches" if graph is None else "CUDA-graph replays of the step (as the reference replays decode)",
+            "timing": {"timed_region": timed_region,
                        "eager_ms_per_step": eager_ms_per_step, "roofline_kernel_ms_from": kernel_ms_from,
                        "eager_decode_ms_median": statistics.median(decode_ms)},
             "self_check_max_abs_err": err,
