@@ -219,12 +219,12 @@ def apply_patches(cfg: dict) -> None:
         _patch_b200(cfg)
     elif cfg["backend"] == "oracle":
         _patch_cpu_debug(cfg)
-    if cfg.get("prefix_cache") or cfg.get("wire") == "delta":
-        from benchmarks import ref_patches
-        if cfg.get("prefix_cache"):
-            ref_patches.patch_prefix_reuse()
-        if cfg.get("wire") == "delta":
-            ref_patches.patch_delta_wire()
+    if cfg.get("prefix_cache"):          # SURVEY.md 8 f-1 (either arm): admission-time radix-tree reuse + cache_sequence fixes
+        from nanovllmx_b200.core import prefix_reuse
+        prefix_reuse.install()
+    if cfg.get("wire") == "delta":       # SURVEY.md 8 f-2 (either arm): per-step delta messages over the reference's own queues
+        from nanovllmx_b200.core import wire_binding
+        wire_binding.install()
     if cfg.get("stats_path"):
         _patch_stats(cfg)
 
@@ -267,7 +267,7 @@ async def run(cfg: dict) -> dict:
     if cfg["workload"] == "bench":
         prompts, max_tokens, max_new = bench_workload(cfg["num_seqs"])
     else:
-        prompts, max_tokens, max_new = shared_prefix_workload(cfg["num_seqs"])
+        prompts, max_tokens, max_new = shared_prefix_workload(cfg["num_seqs"], cfg.get("prefix_len", 2048), cfg.get("gen", 128))
     tp = cfg["tp"]
     t_init = time.time()
     llm = LLM(model=cfg["model_dir"], gpu_memory_utilization=0.8, max_bs=cfg["max_bs"], tp_size=tp, pp_size=1,
@@ -288,6 +288,11 @@ async def run(cfg: dict) -> dict:
 
     warm = []
     await _consume(llm.generate("Benchmark: ", SamplingParams(max_tokens=10)), warm)       # bench.py:31
+    if cfg["workload"] == "shared-prefix":
+        # the system prompt has been served once before the measured requests arrive (the reference inserts a sequence
+        # into the radix tree when it FINISHES, core/scheduler.py:189): one priming request, in every arm
+        await _consume(llm.generate(list(prompts[0][:cfg.get("prefix_len", 2048)]) + [1, 2, 3],
+                                    SamplingParams(max_new_tokens=1, ignore_eos=True, temperature=1.0, top_k=1)), warm)
     init_s = time.time() - t_init
     runs = []
     tokens_runs = []
@@ -324,6 +329,8 @@ def main():
     ap.add_argument("--b200-sampler", action="store_true")
     ap.add_argument("--prefix-cache", action="store_true")
     ap.add_argument("--wire", default="pickle", choices=["pickle", "delta"])
+    ap.add_argument("--prefix-len", type=int, default=2048, help="shared-prefix workload: tokens of the common system prompt")
+    ap.add_argument("--gen", type=int, default=128, help="shared-prefix workload: new tokens per request")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--init-std", type=float, default=0.02)
     ap.add_argument("--nccl-port", type=int, default=29511)
@@ -338,7 +345,7 @@ def main():
                max_bs=a.max_bs, context_len=a.context_len, workload=a.workload, runs=a.runs, greedy=a.greedy or a.argmax, argmax=a.argmax,
                enforce_eager=a.enforce_eager or a.backend == "oracle", fused_qk=a.fused_qk, b200_sampler=a.b200_sampler,
                prefix_cache=a.prefix_cache, wire=a.wire, seed=a.seed, init_std=a.init_std, nccl_port=a.nccl_port,
-               verbose=a.verbose, device_ids=[int(x) for x in a.device_ids.split(",")] if a.device_ids else None)
+               verbose=a.verbose, prefix_len=a.prefix_len, gen=a.gen, device_ids=[int(x) for x in a.device_ids.split(",")] if a.device_ids else None)
     if a.stats:
         cfg["stats_path"] = (a.out or "/tmp/ref_engine") + ".steps.json"
     os.environ[CFG_ENV] = json.dumps(cfg)

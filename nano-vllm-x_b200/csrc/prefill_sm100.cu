@@ -54,31 +54,60 @@ constexpr int kWsOffQ = 0;                           // 2 x 32 KiB
 constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
 constexpr float kLazyTau = 8.0f;
 
-// One softmax step of one row (thread) over a 128-column S tile held in TMEM.
-// MASK is a template parameter so the (rare) masked tiles do not tax the common path with
-// predicated-off instructions (nvcc if-converts a runtime `if` around the element loop).
-template <bool MASK, int NCH = 4>
-__device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
-                                             const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
-                                             const uint32_t bar_p1) {
-  // NCH (masked tiles only, tile-uniform): number of 32-column chunks of S that hold any valid column of this
-  // query tile.  The MMA issuer trims QK to N = 32*NCH and PV to K = 32*NCH, so chunks >= NCH are neither
-  // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
-  static_assert(MASK || NCH == 4, "only masked tiles are trimmed");
-  uint32_t sv[NCH][32];
+// Rare path of the lazy rescale (a row max grew by more than 2^kLazyTau): O_t *= alpha in TMEM.  Kept out of line
+// so that its 32-register O chunk never competes with the 128 S values of the hot path for registers.
+__device__ __noinline__ void rescale_o(const uint32_t tO, const float alpha) {
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t ov[32];
+    tmem_ld_32x32b_x32(tO + c * 32, ov);
+    tmem_wait_ld();
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+    for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
+    tmem_st_32x32b_x32(tO + c * 32, ov);
+  }
+  tmem_wait_st();
+  tc_fence_before();
+}
+
+// 8 P values (tokens 8c..8c+7 of a 64-token half) of this thread's row -> the SWIZZLE_128B K-major P block
+// (row r: 128 bytes at r*128, 16-byte chunk c at (c ^ (r & 7)) << 4): conflict-free STS.128, the layout the PV
+// MMA's A descriptor reads.
+__device__ __forceinline__ void p_store_chunk(const uint32_t p_row, const int r7, const int c, const uint32_t w0, const uint32_t w1,
+                                              const uint32_t w2, const uint32_t w3) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(p_row + (uint32_t)((c ^ r7) << 4)), "r"(w0), "r"(w1), "r"(w2), "r"(w3)
+               : "memory");
+}
+
+// One softmax step of one row (thread) over a 128-column S tile held in TMEM.
+//   1. S_t -> registers, then bar_sfree: the MMA warp may overwrite S_t with QK_t(j+1) at once (it runs UNDER this
+//      tile's exponentials; S and P used to alias in TMEM, which chained softmax(j) -> PV(j) -> QK(j+1) -> softmax(j+1)
+//      and left the tensor pipe idle for half of every tile period: profiles/r1_s38_*).
+//   2. P_t goes to a 16 KiB shared-memory block in two 64-token halves; each half is handed to the MMA warp as soon
+//      as it is written (bar_p0 / bar_p1) and the block is reused for the second half once PV of the first has read
+//      it (bar_pfree: one tcgen05.commit per PV half).
+// MASK is a template parameter so the (rare) masked tiles do not tax the common path with predicated-off
+// instructions (nvcc if-converts a runtime `if` around the element loop).
+template <bool MASK>
+__device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const float scale_log2,
+                                             float& m_used, float& l_run, const uint32_t p_row, const int r7, const uint32_t bar_sfree,
+                                             const uint32_t bar_p0, const uint32_t bar_p1, const uint32_t bar_pfree, int& pfc) {
+  uint32_t sv[4][32];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
   tmem_wait_ld();
+  tc_fence_before();
+  mbar_arrive(bar_sfree);                  // S_t is in registers: QK_t(j+1) may land
   if (MASK) {
 #pragma unroll
-    for (int c = 0; c < NCH; ++c)
+    for (int c = 0; c < 4; ++c)
 #pragma unroll
       for (int e = 0; e < 32; ++e)
         if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
   }
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) {
+  for (int c = 0; c < 4; ++c) {
 #pragma unroll
     for (int e = 0; e < 32; e += 4) {
       mx0 = fmaxf(mx0, __uint_as_float(sv[c][e]));
@@ -97,17 +126,29 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
     alpha = fast_exp2(m_used - mx);
     m_used = mx;
   }
-  const bool rescale = first_pv_done && __any_sync(0xffffffffu, grow);   // warp-uniform, rare (lazy threshold 2^8)
+  const bool rescale = __any_sync(0xffffffffu, grow);   // warp-uniform, rare (lazy threshold 2^8)
   const float neg_m = -m_used;
   float s0 = 0.f, s1 = 0.f;
-  // The O rescale sits AFTER the exponentials in its own (rare) branch: with the rescale ahead of them ptxas
-  // hoists all 128 ex2 above it and spills 15 registers around the 32-register O chunk on the hot path.
+  // Before the first P chunk of a half is stored: the PV MMAs that read the block's previous contents are done
+  // (PV half #(pfc-1), counted over the whole kernel), and -- first half only -- O_t carries the scale P assumes.
+  auto before_half = [&](int half) {
+    if (pfc > 0) mbar_wait(bar_pfree, (pfc - 1) & 1);
+    ++pfc;
+    if (half == 0 && rescale) rescale_o(tO, alpha);
+  };
+  auto after_half = [&](int half) {
+    fence_proxy_async_smem();              // generic-proxy stores -> visible to the tensor core's async-proxy reads
+    mbar_arrive(half ? bar_p1 : bar_p0);
+  };
   if constexpr (!MASK) {
     // Unmasked tiles (the common case): explicit software pipeline over the 128 elements.  The scale FMA runs
     // kAhead elements ahead of its MUFU.EX2, the row-sum add and the bf16 pack kAhead elements behind it, so every
     // MUFU (one per 8 clk per scheduler) has independent FMA-pipe work beside it.
     constexpr int kAhead = 12;
-    uint32_t pw[64];
+    uint32_t pw[32];     // the packed P of one 64-token half: stored in one go at the END of the half, ~1000 clk after the
+                         // previous half was handed over, so the bar_pfree wait in before_half() has long been satisfied
+                         // (storing chunk by chunk put that wait 8 elements behind the hand-over: the softmax warps spent
+                         // 38 % of their samples on it, profiles/r2_s5_*)
 #pragma unroll
     for (int e = 0; e < kAhead; ++e)
       sv[e >> 5][e & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[e >> 5][e & 31]), scale_log2, neg_m));
@@ -123,15 +164,12 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
         const int d = e - kAhead;
         if (d & 1) {
           s1 = add_ordered(s1, __uint_as_float(sv[d >> 5][d & 31]));
-          pw[d >> 1] = pack_bf16x2_ordered(__uint_as_float(sv[(d - 1) >> 5][(d - 1) & 31]), __uint_as_float(sv[d >> 5][d & 31]));
-          if ((d & 31) == 31) {
-            const int c = d >> 5;
-            tmem_st_32x32b_x16(tS + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&pw[c * 16]));   // P: packed bf16x2 over S
-            if (!rescale && (c == 1 || c == 3)) {     // hand P over in two halves: PV starts on the first
-              tmem_wait_st();
-              tc_fence_before();
-              mbar_arrive(c == 1 ? bar_p0 : bar_p1);
-            }
+          pw[(d >> 1) & 31] = pack_bf16x2_ordered(__uint_as_float(sv[(d - 1) >> 5][(d - 1) & 31]), __uint_as_float(sv[d >> 5][d & 31]));
+          if ((d & 63) == 63) {
+            before_half(d >> 6);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) p_store_chunk(p_row, r7, c, pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
+            after_half(d >> 6);
           }
         } else {
           s0 = add_ordered(s0, __uint_as_float(sv[d >> 5][d & 31]));
@@ -140,44 +178,25 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
     }
   } else {
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    uint32_t pw[16];
+    for (int half = 0; half < 2; ++half) {
+      uint32_t pw[32];
 #pragma unroll
-    for (int e = 0; e < 16; ++e) {
-      const float a = exp2_fma(__uint_as_float(sv[c][2 * e]), scale_log2, neg_m);
-      const float b = exp2_fma(__uint_as_float(sv[c][2 * e + 1]), scale_log2, neg_m);
-      s0 += a;
-      s1 += b;
-      pw[e] = pack_bf16x2(a, b);
-    }
-    tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
-    constexpr int kFirst = NCH > 1 ? 1 : 0;         // hand P over in two halves: PV starts on the first
-    if (!rescale && (c == kFirst || c == NCH - 1)) { // while the second is still in the exp unit
-      tmem_wait_st();
-      tc_fence_before();
-      if (c == kFirst) mbar_arrive(bar_p0);
-      if (c == NCH - 1) mbar_arrive(bar_p1);
-    }
-  }
-  }
-  if (rescale) {                                    // O must carry the new scale before PV(j) accumulates into it
+      for (int e = 0; e < 32; ++e) {
+        const int c = half * 2 + (e >> 4), k = e & 15;
+        const float a = exp2_fma(__uint_as_float(sv[c][2 * k]), scale_log2, neg_m);
+        const float b = exp2_fma(__uint_as_float(sv[c][2 * k + 1]), scale_log2, neg_m);
+        s0 += a;
+        s1 += b;
+        pw[e] = pack_bf16x2(a, b);
+      }
+      before_half(half);
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      uint32_t ov[32];
-      tmem_ld_32x32b_x32(tO + c * 32, ov);
-      tmem_wait_ld();
-#pragma unroll
-      for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
-      tmem_st_32x32b_x32(tO + c * 32, ov);
+      for (int c = 0; c < 8; ++c) p_store_chunk(p_row, r7, c, pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
+      after_half(half);
     }
-    tmem_wait_st();
-    tc_fence_before();
-    mbar_arrive(bar_p0);
-    mbar_arrive(bar_p1);
   }
   l_run = l_run * alpha + (s0 + s1);
 }
-
 
 // =====================================================================================================
 // The pipeline is PERSISTENT.
@@ -205,8 +224,9 @@ constexpr int kPlanThreads = 1024;
 constexpr int kPlanBuckets = 1024;
 constexpr int kWorkHeaderInts = 16;     // [0] work counter, [1] number of (sequence, tile) pairs
 // Dynamic shared memory: 2 Q tiles + 4-slot K/V ring + one 32 KiB tile the softmax warps stage output rows in.
-constexpr int kWsOffStage = kWsOffRing + kRing * kTileBytes2;   // persistent kernel only
-constexpr int kPersistSmem = kWsOffStage + kTileBytes2 + 1024;
+constexpr int kWsOffP = kWsOffRing + kRing * kTileBytes2;       // P_0, P_1: one [128 x 64] bf16 block (16 KiB) per query tile
+constexpr int kWsOffStage = kWsOffP;                            // the epilogue stages output rows in the (then idle) P blocks
+constexpr int kPersistSmem = kWsOffP + 2 * kBlkBytes + 1024;
 
 struct ItemDesc {
   int s, kvh, j0, Lq, Lkv, q0, page0, valid;
@@ -284,24 +304,15 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
                                                                                const __grid_constant__ CUtensorMap tm_v) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing];
+  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing + 4];
   __shared__ __align__(16) ItemDesc s_items[kItemRing];
+  __shared__ __align__(16) int s_slots[2][2][2][32];   // cp.async producers: [tile parity][warp][row parity][i]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool tma_kv = p.log2_ps >= 4;                  // K/V tiles by TMA (page_size >= 16) or by cp.async gathers
   const int G = 1 << log2_g;
   const int tok_per_tile = kTM >> log2_g;
   const int tok_per_cta = 2 * tok_per_tile;
-  // Trimmed last tiles: 32-column chunks of KV tile j that hold columns below the query tile's kv_hi.  Bench-shaped
-  // prompts (100..1024 tokens) own 1..8 KV tiles per item and the last one of each query tile is only
-  // partly valid (causal diagonal of a 32/64-token packed tile, ragged sequence end): QK, softmax and PV
-  // run on 32*nch columns instead of 128 (8-12 % of all chunk steps on the bench prompts).
-  // Compile-time switches, set from a same-box A/B on B200 of a build that had them as run-time flags
-  // (profiles/r1_s38_prefill_flags_ab.txt; bench prompts Hq32 / uniform 16x4096 Hq32, fraction of bf16 peak):
-  //   none 0.303 / 0.633   trim 0.298 / 0.640   staged 0.319 / 0.650   lean_q 0.326 / 0.648   all three 0.291 / 0.670
-  // Trimming costs more than it saves on short prompts (four masked-softmax instances; the kernel is ~7000 SASS
-  // instructions and every extra hot path shows), so it stays off; dead branches are removed by the compiler.
-  constexpr bool trim = false, staged = true, lean_q = true;
-  auto chunks_of = [&](int kv_hi, int j) { return trim ? min(4, (kv_hi - j * kTN + 31) >> 5) : 4; };
 
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
@@ -313,13 +324,15 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   auto bar_o = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 6 + t); };
   auto bar_ifull = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + slot); };
   auto bar_iempty = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + kItemRing + slot); };
+  auto bar_sfree = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + t); };      // S_t is in registers
+  auto bar_pfree = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + 2 + t); };  // a PV half has read P_t
   constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 TMA warps (lane 0 of each arrives)
 
   if (tid == 0) {
     mbar_init(bar_q, 1);              // one arrive.expect_tx by the TMA warp + the transaction bytes
     mbar_init(bar_qfree, 1);
     for (int i = 0; i < kRing; ++i) {
-      mbar_init(bar_full(i), 1);
+      mbar_init(bar_full(i), tma_kv ? 1 : 64);   // TMA: one arrive.expect_tx + bytes; cp.async: the 64 producer threads
       mbar_init(bar_empty(i), 1);
     }
     for (int t = 0; t < 2; ++t) {
@@ -327,6 +340,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_init(bar_p(t, 0), 128);
       mbar_init(bar_p(t, 1), 128);
       mbar_init(bar_o(t), 1);
+      mbar_init(bar_sfree(t), 128);
+      mbar_init(bar_pfree(t), 1);
     }
     for (int i = 0; i < kItemRing; ++i) {
       mbar_init(bar_ifull(i), 1);
@@ -386,82 +401,214 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       if (!valid) break;
     }
   } else if (warp >= 9) {
-    // =================================== TMA producers =====================================================
-    // Warp 9 stages Q and the K tiles, warp 10 the V tiles (ring slots alternate K0 V0 K1 V1 ...).
-    // Q: four tiled 3-D boxes per item ([64 d] x [G heads] x [128/G tokens]: two query tiles x two 64-column halves;
-    // rows past the sequence / past T are other tokens or zero fill and their outputs are never stored).
-    // K/V: tile::gather4 through the page table -- lane l owns tile rows 4l..4l+3, so a 128-token tile is 2
-    // instructions per lane (one per 64-column half): 64 TMA instructions per tile instead of 2048 LDGSTS.  ptxas
-    // issues a per-lane instruction with lane-varying operands as a 32-trip elect loop (~14 instructions per trip),
-    // which is why K and V have a warp each.  Rows past the end of the sequence re-read its last valid slot
-    // (finite data; their S columns are masked to -inf, their P is exactly 0).  Completion is counted in bytes on
-    // the ring's mbarriers (arrive.expect_tx).
+    // =================================== producers (warps 9, 10) ==========================================
+    // Q, always TMA: four tiled 3-D boxes per item ([64 d] x [G heads] x [128/G tokens]: two query tiles x two
+    // 64-column halves), issued by one thread; rows past the sequence / past T are other tokens or zero fill and their
+    // outputs are never stored.
+    // K/V ring order: K(0), then K(j+1) ahead of V(j) -- QK(j+1) is issued a whole tile period before PV(j).
+    //   * page_size >= 16: TMA.  Warp 9 stages the K tiles, warp 10 the V tiles, tile::gather4 through the page table
+    //     (lane l owns tile rows 4l..4l+3: 2 instructions per lane per tile; completion counted in bytes on the ring's
+    //     mbarriers).  Rows past the end of the sequence re-read its last valid slot (finite data; their S columns are
+    //     masked to -inf, their P is exactly 0).
+    //   * page_size < 16 (the reference's token-granular mode, page_size 1): 16-byte cp.async gathers by both warps,
+    //     zero fill past the end.  MEASURED: gather4 needs 64 instructions per tile, each a 14-instruction elect loop
+    //     trip on the uniform datapath (~90 clk); two producer warps were 85 % busy issuing and the kernel fell from
+    //     0.69 to 0.46 of bf16 peak on 16 x 4096 (profiles/r2_s4_*gather4*).  2048 LDGSTS per tile cost ~8 clk per warp
+    //     instruction, a twentieth of that, so a per-token gather stays on the LSU path; the bytes are laid out exactly as
+    //     TMA SWIZZLE_128B would write them.
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
     const int ps_mask = (1 << p.log2_ps) - 1;
-    const int is_v = warp - 9;                       // 0: Q + K tiles, 1: V tiles
-    const CUtensorMap* tm = is_v ? &tm_v : &tm_k;
+    const int lw = warp - 9;
+    const uint32_t smem_q = smem + kWsOffQ, smem_ring = smem + kWsOffRing;
     if (lane == 0) {
-      tma::prefetch_desc(tm);
-      if (!is_v) tma::prefetch_desc(&tm_q);
+      if (lw == 0) tma::prefetch_desc(&tm_q);
+      if (tma_kv) tma::prefetch_desc(lw ? &tm_v : &tm_k);
     }
-    int fill = is_v, qn = 0;                         // running ring-fill index of this warp's next tile
-    for (int it = 0;; ++it) {
-      const ItemDesc d = take_item(it);
-      if (!d.valid) break;
-      const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
-      if (g.J == 0) continue;
-      const uint32_t smem_q = smem + kWsOffQ, smem_ring = smem + kWsOffRing;
-      const int last_tok = g.kv_hi_all - 1;
-      const int last_slot = (__ldg(p.kv_indices + d.page0 + (last_tok >> p.log2_ps)) << p.log2_ps) + (last_tok & ps_mask);
-      int sl[4], sn[4];
-      auto ldg_slots = [&](int tile, int (&dst)[4]) {
+    int qn = 0;
+    if (tma_kv) {
+      const CUtensorMap* tm = lw ? &tm_v : &tm_k;
+      int fill = lw;                                   // running ring-fill index of this warp's next tile
+      for (int it = 0;; ++it) {
+        const ItemDesc d = take_item(it);
+        if (!d.valid) break;
+        const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
+        if (g.J == 0) continue;
+        const int last_tok = g.kv_hi_all - 1;
+        const int last_slot = (__ldg(p.kv_indices + d.page0 + (last_tok >> p.log2_ps)) << p.log2_ps) + (last_tok & ps_mask);
+        int sl[4], sn[4];
+        auto ldg_slots = [&](int tile, int (&dst)[4]) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int tok = tile * kTN + 4 * lane + i;
-          dst[i] = tok <= last_tok ? (__ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps)) << p.log2_ps) + (tok & ps_mask) : last_slot;
+          for (int i = 0; i < 4; ++i) {
+            const int tok = tile * kTN + 4 * lane + i;
+            dst[i] = tok <= last_tok ? (__ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps)) << p.log2_ps) + (tok & ps_mask) : last_slot;
+          }
+        };
+        ldg_slots(0, sl);
+        if (lw == 0 && lane == 0) {
+          mbar_wait(bar_qfree, (qn & 1) ^ 1);
+          tma::mbar_expect_tx(bar_q, 2 * kTileBytes2);
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              tma::load_3d(smem_q + t * kTileBytes2 + h * kBlkBytes, &tm_q, bar_q, h * 64, d.kvh * G, d.q0 + d.j0 + t * tok_per_tile);
+        }
+        ++qn;
+        const int col = d.kvh * kTD;
+        for (int tile = 0; tile < g.J; ++tile, fill += 2) {
+          const int slot = fill % kRing, use = fill / kRing;
+          if (tile + 1 < g.J) ldg_slots(tile + 1, sn);      // in flight behind this tile's issue loop
+          mbar_wait(bar_empty(slot), (use & 1) ^ 1);
+          const uint32_t full = bar_full(slot);
+          if (lane == 0) tma::mbar_expect_tx(full, kTileBytes2);
+          __syncwarp();
+          const uint32_t dst = smem_ring + slot * kTileBytes2 + lane * 512;
+          tma::gather4(dst, tm, full, col, sl[0], sl[1], sl[2], sl[3]);
+          tma::gather4(dst + kBlkBytes, tm, full, col + 64, sl[0], sl[1], sl[2], sl[3]);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) sl[i] = sn[i];
+        }
+      }
+    } else {
+      const int lt = tid - 9 * 32;                    // 0..63
+      const int gc = lt & 15, lrow0 = lt >> 4;        // 16-byte column gc of rows lrow0 + 4*i
+      const uint32_t chunk_off = (uint32_t)(gc >> 3) * kBlkBytes;
+      const int c8 = gc & 7;
+      const int hrow = lane >> 4;
+      const uint32_t stride_b = (uint32_t)(p.kv_slot_stride * 2);   // bytes between token slots (< 4 GiB)
+      const uint32_t dst_even = chunk_off + lrow0 * 128 + ((c8 ^ lrow0) << 4);
+      const uint32_t dst_odd = chunk_off + lrow0 * 128 + ((c8 ^ (lrow0 + 4)) << 4);
+      // One cp.async group per fill.  A fill's mbarrier is signalled when the NEXT fill has been issued
+      // (wait_group 1), so one fill is always in flight; before blocking on anything that may depend on the
+      // consumers, the pending fill is flushed.
+      uint32_t pend_bar = 0;
+      auto rotate = [&](uint32_t this_bar) {
+        cp_async_commit();
+        cp_async_wait<1>();
+        fence_proxy_async_smem();
+        if (pend_bar) mbar_arrive(pend_bar);
+        pend_bar = this_bar;
+      };
+      auto flush = [&]() {
+        cp_async_wait<0>();
+        fence_proxy_async_smem();
+        if (pend_bar) mbar_arrive(pend_bar);
+        pend_bar = 0;
+      };
+      auto wait_or_flush = [&](uint32_t bar, uint32_t parity) {
+        if (!mbar_test_wait(bar, parity)) {
+          flush();
+          mbar_wait(bar, parity);
         }
       };
-      ldg_slots(0, sl);
-      // ---- Q: 256 packed rows; row R of tile t = (token j0 + t*tok_per_tile + R / G, head kvh*G + R % G) ---------
-      if (!is_v && lane == 0) {
-        mbar_wait(bar_qfree, (qn & 1) ^ 1);
-        tma::mbar_expect_tx(bar_q, 2 * kTileBytes2);
+      int kc = 0, vc = 0;                              // K / V tiles filled so far (whole kernel)
+      for (int it = 0;; ++it) {
+        wait_or_flush(bar_ifull(it % kItemRing), (it / kItemRing) & 1);
+        const ItemDesc d = take_item(it);
+        if (!d.valid) break;
+        const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
+        if (g.J == 0) continue;
+        // slot ids of a tile: this thread resolves tokens 4*lane + 2*lw (+1) and parks them in shared memory, where
+        // the 32 rows it copies (lrow0 + 4i) find theirs; two tiles are resident (K runs one tile ahead of V)
+        int pg_a = -1, pg_b = -1;
+        auto ldg_pages = [&](int tile) {
+          const int tok = tile * kTN + 4 * lane + 2 * lw;
+          pg_a = pg_b = -1;
+          if (tok < g.kv_hi_all) pg_a = __ldg(p.kv_indices + d.page0 + (tok >> p.log2_ps));
+          if (tok + 1 < g.kv_hi_all) pg_b = __ldg(p.kv_indices + d.page0 + ((tok + 1) >> p.log2_ps));
+        };
+        auto put_slots = [&](int tile) {
+          const int tok = tile * kTN + 4 * lane + 2 * lw;
+          s_slots[tile & 1][lw][0][lane] = pg_a >= 0 ? (pg_a << p.log2_ps) + (tok & ps_mask) : -1;
+          s_slots[tile & 1][lw][1][lane] = pg_b >= 0 ? (pg_b << p.log2_ps) + ((tok + 1) & ps_mask) : -1;
+        };
+        ldg_pages(0);
+        wait_or_flush(bar_qfree, (qn & 1) ^ 1);
+        if (lt == 0) {
+          tma::mbar_expect_tx(bar_q, 2 * kTileBytes2);
 #pragma unroll
-        for (int t = 0; t < 2; ++t)
+          for (int t = 0; t < 2; ++t)
 #pragma unroll
-          for (int h = 0; h < 2; ++h)
-            tma::load_3d(smem_q + t * kTileBytes2 + h * kBlkBytes, &tm_q, bar_q, h * 64, d.kvh * G, d.q0 + d.j0 + t * tok_per_tile);
+            for (int h = 0; h < 2; ++h)
+              tma::load_3d(smem_q + t * kTileBytes2 + h * kBlkBytes, &tm_q, bar_q, h * 64, d.kvh * G, d.q0 + d.j0 + t * tok_per_tile);
+        }
+        ++qn;
+        __syncwarp();                                    // every lane is done reading the previous item's slot ids
+        put_slots(0);
+        if (g.J > 1) {
+          ldg_pages(1);
+          put_slots(1);
+        }
+        const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)d.kvh * kTD + gc * 8);
+        const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)d.kvh * kTD + gc * 8);
+        auto fill_tile = [&](const char* base, int tile, int slot, int use) {
+          __syncwarp();
+          int sl[32];
+          const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int4 v = src[i];
+            sl[4 * i] = v.x; sl[4 * i + 1] = v.y; sl[4 * i + 2] = v.z; sl[4 * i + 3] = v.w;
+          }
+          wait_or_flush(bar_empty(slot), (use & 1) ^ 1);
+          const uint32_t dst0 = smem_ring + slot * kTileBytes2;
+          if ((tile + 1) * kTN <= g.kv_hi_all) {            // full tile: no zero-fill predicates
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)sl[i] * stride_b, 16u);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const bool ok = sl[i] >= 0;
+              cp_async_16(dst0 + ((i & 1) ? dst_odd : dst_even) + i * 512, base + (uint64_t)(uint32_t)(ok ? sl[i] : 0) * stride_b,
+                          ok ? 16u : 0u);
+            }
+          }
+          rotate(bar_full(slot));
+        };
+        fill_tile(kbase, 0, 2 * (kc & 1), kc >> 1);
+        ++kc;
+        for (int j = 0; j < g.J; ++j) {
+          if (j + 2 < g.J) ldg_pages(j + 2);               // consumed after V(j) has been issued
+          if (j + 1 < g.J) {
+            fill_tile(kbase, j + 1, 2 * (kc & 1), kc >> 1);
+            ++kc;
+          }
+          fill_tile(vbase, j, 2 * (vc & 1) + 1, vc >> 1);
+          ++vc;
+          if (j + 2 < g.J) {
+            __syncwarp();                                  // V(j) has read tile j's slot ids: its parity is free
+            put_slots(j + 2);
+          }
+        }
       }
-      ++qn;
-      const int col = d.kvh * kTD;
-      for (int tile = 0; tile < g.J; ++tile, fill += 2) {
-        const int slot = fill % kRing, use = fill / kRing;
-        if (tile + 1 < g.J) ldg_slots(tile + 1, sn);      // in flight behind this tile's issue loop
-        mbar_wait(bar_empty(slot), (use & 1) ^ 1);
-        const uint32_t full = bar_full(slot);
-        if (lane == 0) tma::mbar_expect_tx(full, kTileBytes2);
-        __syncwarp();
-        const uint32_t dst = smem_ring + slot * kTileBytes2 + lane * 512;
-        tma::gather4(dst, tm, full, col, sl[0], sl[1], sl[2], sl[3]);
-        tma::gather4(dst + kBlkBytes, tm, full, col + 64, sl[0], sl[1], sl[2], sl[3]);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) sl[i] = sn[i];
-      }
+      flush();
     }
   } else if (warp == 8) {
     // =================================== MMA issuer =======================================================
+    // Issue order per KV tile j:   QK_0(j+1) QK_1(j+1)   PV_0(j) PV_1(j)
+    // QK(j+1) needs only K(j+1) and S_t to be free, which the softmax group signals right after it has pulled
+    // S_t(j) into registers, so the tensor pipe computes the NEXT scores under the CURRENT tile's exponentials and the
+    // softmax groups never wait for a QK in steady state.  PV_t(j) follows P_t(j) half by half (two 64-token halves
+    // through one shared-memory block per query tile; A and B both from shared memory).
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    constexpr uint32_t idesc_qk0 = make_idesc_bf16_f32(kTM, 0, 0, 0);             // N field filled per tile
+    constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
     constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
     const uint64_t qdesc0 = make_smem_desc(smem + kWsOffQ, 16, 1024);
     const uint64_t kdesc0 = make_smem_desc(smem + kWsOffRing, 16, 1024);          // K tiles: K-major
     const uint64_t vdesc0 = make_smem_desc(smem + kWsOffRing, kBlkBytes, 1024);   // V tiles: MN-major
-    // f = running ring-fill index of the K tile; nch = 32-column chunks of S to produce (N = 32 * nch: the
-    // first N token rows of the K-major tile)
-    auto issue_qk = [&](int t, int f, int nch) {
+    const uint64_t pdesc0 = make_smem_desc(smem + kWsOffP, 16, 1024);             // P blocks: K-major, 64 tokens wide
+    int qkc[2] = {0, 0};          // QK_t issued so far (whole kernel) == S_t tiles handed to softmax group t
+    int pc[2] = {0, 0};           // P_t tiles consumed so far
+    // f = running ring-fill index of the K tile
+    auto issue_qk = [&](int t, int f) {
+      if (qkc[t] > 0) {                                  // softmax group t has read the previous S_t out of TMEM
+        mbar_wait(bar_sfree(t), (qkc[t] - 1) & 1);
+        tc_fence_after();
+      }
+      ++qkc[t];
       const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
       const uint64_t kd = kdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
-      const uint32_t idesc_qk = idesc_qk0 | ((uint32_t)(nch << 2) << 17);
 #pragma unroll
       for (int ks = 0; ks < kTD / 16; ++ks) {
         const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
@@ -469,17 +616,17 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       }
       umma_commit_elect(bar_s(t));
     };
-    // f = running ring-fill index of the V tile; nks = 16-token K steps holding valid P columns (2 per chunk)
-    auto issue_pv = [&](int t, int f, int half, bool acc, int nks) {
-      const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
+    // f = running ring-fill index of the V tile; half = 64-token half of the tile (4 K steps of 16 tokens)
+    auto issue_pv_half = [&](int t, int f, int half, bool acc) {
+      const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4)) + (uint64_t)(half * 4 * (2048 >> 4));
+      const uint64_t pd = pdesc0 + (uint64_t)(t * (kBlkBytes >> 4));
 #pragma unroll
-      for (int ks = half * 4; ks < half * 4 + 4; ++ks)
-        if (ks < nks)
-          umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
-                        (acc || ks > 0));
+      for (int ks = 0; ks < 4; ++ks)
+        umma_ss_elect(tmem + 2 * kTN + t * kTD, pd + (uint64_t)(ks * (32 >> 4)), vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
+                      (acc || ks > 0));
+      umma_commit_elect(bar_pfree(t));
     };
     int fillc = 0, qn = 0;
-    int pc[2] = {0, 0};
     for (int it = 0;; ++it) {
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
@@ -489,41 +636,37 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_wait(bar_q, qn & 1);
       mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
       tc_fence_after();
-      if (g.nt0 > 0) issue_qk(0, base, chunks_of(g.kvhi0, 0));
-      if (g.nt1 > 0) issue_qk(1, base, chunks_of(g.kvhi1, 0));
+      if (g.nt0 > 0) issue_qk(0, base);
+      if (g.nt1 > 0) issue_qk(1, base);
       umma_commit_elect(bar_empty(base % kRing));                        // K(0) free once both QK(0) are done
       if (g.J == 1) umma_commit_elect(bar_qfree);                        // last QK of the item: Q may be refilled
       for (int j = 0; j < g.J; ++j) {
         const int fv = base + 2 * j + 1, fk = base + 2 * j + 2;
+        if (j + 1 < g.J) {                                               // scores of the NEXT tile, under this tile's softmax
+          mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);             // K(j+1)
+          tc_fence_after();
+          if (j + 1 < g.nt0) issue_qk(0, fk);
+          if (j + 1 < g.nt1) issue_qk(1, fk);
+          umma_commit_elect(bar_empty(fk % kRing));
+          if (j + 2 == g.J) umma_commit_elect(bar_qfree);
+        }
         mbar_wait(bar_full(fv % kRing), (fv / kRing) & 1);               // V(j)
-        bool k_ready = false;
+        tc_fence_after();
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
           const int ntt = t ? g.nt1 : g.nt0;
-          const int kvhit = t ? g.kvhi1 : g.kvhi0;
           if (j < ntt) {
-            const int nks = 2 * chunks_of(kvhit, j);
-            mbar_wait(bar_p(t, 0), pc[t] & 1);                           // first 64 columns of P_t(j) are in TMEM
+            mbar_wait(bar_p(t, 0), pc[t] & 1);                           // tokens 0..63 of P_t(j) are in shared memory
             tc_fence_after();
-            issue_pv(t, fv, 0, j > 0, nks);
-            mbar_wait(bar_p(t, 1), pc[t] & 1);                           // the rest
+            issue_pv_half(t, fv, 0, j > 0);
+            mbar_wait(bar_p(t, 1), pc[t] & 1);                           // tokens 64..127 (same block, rewritten)
             tc_fence_after();
-            issue_pv(t, fv, 1, true, nks);
+            issue_pv_half(t, fv, 1, true);
             ++pc[t];
             if (j == ntt - 1) umma_commit_elect(bar_o(t));
           }
-          if (j + 1 < ntt) {
-            if (!k_ready) {
-              mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);         // K(j+1)
-              tc_fence_after();
-              k_ready = true;
-            }
-            issue_qk(t, fk, chunks_of(kvhit, j + 1));
-          }
         }
         umma_commit_elect(bar_empty(fv % kRing));
-        if (j + 1 < g.J) umma_commit_elect(bar_empty(fk % kRing));
-        if (j + 2 == g.J) umma_commit_elect(bar_qfree);
       }
       fillc += 2 * g.J;
       ++qn;
@@ -536,7 +679,9 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem + lane_base + t * kTN;
     const uint32_t tO = tmem + lane_base + 2 * kTN + t * kTD;
+    const uint32_t p_row = smem + kWsOffP + (uint32_t)t * kBlkBytes + (uint32_t)r * 128u;   // my row of the P_t block
     int sc = 0, oc = 0;
+    int pfc = 0;                                      // P halves written so far (whole kernel)
     for (int it = 0;; ++it) {
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
@@ -555,14 +700,11 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
         if (need_mask) {
           const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
-          switch (chunks_of(kv_hi, j)) {                              // tile-uniform
-            case 1: softmax_tile<true, 1>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-            case 2: softmax_tile<true, 2>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-            case 3: softmax_tile<true, 3>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-            default: softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-          }
+          softmax_tile<true>(tS, tO, nvalid, p.scale_log2, m_used, l_run, p_row, r & 7, bar_sfree(t), bar_p(t, 0), bar_p(t, 1),
+                             bar_pfree(t), pfc);
         } else {
-          softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
+          softmax_tile<false>(tS, tO, kTN, p.scale_log2, m_used, l_run, p_row, r & 7, bar_sfree(t), bar_p(t, 0), bar_p(t, 1),
+                              bar_pfree(t), pfc);
         }
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
@@ -577,45 +719,19 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       // (8 lanes per row); straight from the TMEM layout (thread = row) a warp store touches 32 lines with 16 bytes
       // each and the 8 softmax warps spent ~4000 LSU wavefront-cycles per item in the epilogue (14 % of their
       // time on bench-shaped prompts).  Staging area, 4 KiB per warp (32 rows x 64 columns bf16, 16-byte pieces
-      // XOR-swizzled by row): the 7th operand tile, touched by nobody else.
+      // XOR-swizzled by row): this warp's own 32 rows of the P_t block, idle once bar_o says every PV_t has read it.
       const uint32_t stage = smem + kWsOffStage + (uint32_t)warp * 4096u;
       const int rows_ok = tokst << log2_g;
       const int rsub = lane >> 3, piece = lane & 7;
-      if (!has || !staged) {
-        // thread = row, straight from the TMEM layout.  Rows without any visible KV (Lkv == 0, or causal with
-        // Lkv < Lq) are zeros; with data this is the unstaged form kept for A/B measurements.
-        if (r < rows_ok) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + my_tok) * p.out_row_stride +
-                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
-          if (!has) {
+      if (!has && r < rows_ok) {
+        // rows without any visible KV (Lkv == 0, or causal with Lkv < Lq) are zeros
+        uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + my_tok) * p.out_row_stride +
+                                              (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
 #pragma unroll
-            for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
-          }
-        }
-        if (has) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + (r < rows_ok ? my_tok : d.j0)) * p.out_row_stride +
-                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t ov[32];
-            tmem_ld_32x32b_x32(tO + c * 32, ov);
-            tmem_wait_ld();
-            if (r < rows_ok) {
-#pragma unroll
-              for (int j8 = 0; j8 < 4; ++j8) {
-                uint4 w;
-                w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
-                w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
-                w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
-                w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
-                dst[c * 4 + j8] = w;
-              }
-            }
-          }
-        }
+        for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
       }
 #pragma unroll
-      for (int half = 0; half < 2 && has && staged; ++half) {
+      for (int half = 0; half < 2 && has; ++half) {
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
           uint32_t ov[32];
