@@ -36,6 +36,11 @@ DECODE_CASES = [
     ([4097], 32, 8, 1), ([15, 16, 17, 40, 4000], 32, 8, 16), ([700, 9], 4, 1, 16), ([33, 600], 8, 2, 16),
     ([50] * 300, 16, 8, 1), ([3000] * 40, 16, 8, 1), ([5, 0, 9], 16, 8, 1), ([20000, 10], 32, 8, 16),
     ([129, 64], 8, 8, 1), ([90, 7], 64, 8, 1), ([45, 1100], 6, 3, 1), ([45, 1100], 32, 16, 1),
+    # streams that cross many sequences of 1-3 tiles (the producer cursor runs more than one sequence ahead of the math)
+    ([20] * 50 + [1] * 30 + [40] * 20 + [0, 7, 0, 33], 4, 1, 1), ([2000, 17, 33, 900, 16, 1, 48], 8, 2, 16),
+    ([17, 0, 0, 35, 16, 15, 700, 1, 1, 1, 2, 64], 32, 8, 1),
+    # more sequences than the shared-memory tile prefix holds (4096): the warp-scan locate path
+    ([3] * 3000 + [21] * 1500, 8, 8, 1), ([5] * 4200, 4, 1, 1),
 ]
 
 
