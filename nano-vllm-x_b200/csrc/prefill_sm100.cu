@@ -20,6 +20,10 @@
 #include "sm100.cuh"
 #include "tma.cuh"
 
+#ifndef B200_PREFILL_EMU_PAIRS
+#define B200_PREFILL_EMU_PAIRS 1
+#endif
+
 namespace b200 {
 
 using namespace sm100;
@@ -49,7 +53,7 @@ constexpr int kTileBytes2 = 2 * kBlkBytes;     // a full [128 x 128] bf16 operan
 // (exact: O and l carry the same stale scale until the final division).
 // =====================================================================================================
 constexpr int kWsThreads = 384;   // 3 warpgroups: softmax0, softmax1, {MMA, 2 loaders, 1 spare}
-constexpr int kRing = 4;
+constexpr int kRing = 3;                             // K(j+1), V(j) in use + one tile in flight; filled in consumption order
 constexpr int kWsOffQ = 0;                           // 2 x 32 KiB
 constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
 constexpr float kLazyTau = 8.0f;
@@ -79,19 +83,85 @@ __device__ __forceinline__ void p_store_chunk(const uint32_t p_row, const int r7
                : "memory");
 }
 
+// ---- packed f32x2 helpers (FFMA2 / FADD2 on sm_100) and the FMA-pipe exponential --------------------------------
+// All arithmetic forms are `asm volatile`: together with bar.warp.sync fences they pin the instruction ORDER of the
+// softmax software pipeline (ptxas keeps volatile asm in program order); the mov.b64 pack / unpack forms are plain
+// register-pair aliases and cost no instruction.
+constexpr int kEmuPairs = B200_PREFILL_EMU_PAIRS;   // of every 4 element pairs, how many take the FMA-pipe exponential
+static_assert(kEmuPairs >= 0 && kEmuPairs <= 2, "B200_PREFILL_EMU_PAIRS must be 0, 1 or 2");
+__device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, uint32_t& lo, uint32_t& hi) {
+  asm("mov.b64 {%0, %1}, %2;\n" : "=r"(lo), "=r"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2_ordered(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm volatile("fma.rn.f32x2 %0, %1, %2, %3;\n" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2_ordered(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm volatile("add.rn.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2_rm_ordered(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm volatile("add.rm.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t sub2_ordered(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm volatile("sub.rn.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// exp2 on the FMA pipe (the FlashAttention-4 scheme): y = n + f, n = floor(y) (add.rm against 1.5 * 2^23 leaves n in the
+// low mantissa bits), 2^f by a degree-3 polynomial on [0, 1) (max relative error 8.8e-5, far inside bf16's 2^-9; p(0) == 1
+// exactly, so the row maximum still maps to 1), then n is added into the exponent field.  y is clamped at -126 first (the
+// result of anything below is a denormal P that bf16 flushes anyway).
+#define B200_F2X(bits) ((uint64_t)(bits) | ((uint64_t)(bits) << 32))
+constexpr uint64_t kMagic2 = B200_F2X(0x4B400000u);   // 12582912.0f = 1.5 * 2^23
+constexpr uint64_t kPolyC0 = B200_F2X(0x3F800000u);   // 1.0
+constexpr uint64_t kPolyC1 = B200_F2X(0x3F31F519u);   // 0.695146143436431884765625
+constexpr uint64_t kPolyC2 = B200_F2X(0x3E6906A4u);   // 0.227564394474029541015625
+constexpr uint64_t kPolyC3 = B200_F2X(0x3D9DF09Du);   // 0.077119089663028717041015625
+__device__ __forceinline__ uint64_t clamp_lo_ordered(uint64_t v) {
+  uint64_t r;
+  asm volatile("{\n\t.reg .f32 a, b;\n\tmov.b64 {a, b}, %1;\n\tmax.f32 a, a, 0fC2FC0000;\n\tmov.b64 %0, {a, b};\n\t}\n" : "=l"(r) : "l"(v));
+  return r;
+}
+__device__ __forceinline__ uint64_t clamp_hi_ordered(uint64_t v) {
+  uint64_t r;
+  asm volatile("{\n\t.reg .f32 a, b;\n\tmov.b64 {a, b}, %1;\n\tmax.f32 b, b, 0fC2FC0000;\n\tmov.b64 %0, {a, b};\n\t}\n" : "=l"(r) : "l"(v));
+  return r;
+}
+__device__ __forceinline__ uint64_t exp2_combine_ordered(uint64_t p, uint64_t t) {
+  uint64_t r;
+  asm volatile(
+      "{\n\t.reg .b32 a, b, c, d;\n\tmov.b64 {a, b}, %1;\n\tmov.b64 {c, d}, %2;\n\t"
+      "shl.b32 c, c, 23;\n\tshl.b32 d, d, 23;\n\tadd.s32 a, a, c;\n\tadd.s32 b, b, d;\n\tmov.b64 %0, {a, b};\n\t}\n"
+      : "=l"(r)
+      : "l"(p), "l"(t));
+  return r;
+}
+
 // One softmax step of one row (thread) over a 128-column S tile held in TMEM.
 //   1. S_t -> registers, then bar_sfree: the MMA warp may overwrite S_t with QK_t(j+1) at once (it runs UNDER this
 //      tile's exponentials; S and P used to alias in TMEM, which chained softmax(j) -> PV(j) -> QK(j+1) -> softmax(j+1)
 //      and left the tensor pipe idle for half of every tile period: profiles/r1_s38_*).
-//   2. P_t goes to a 16 KiB shared-memory block in two 64-token halves; each half is handed to the MMA warp as soon
-//      as it is written (bar_p0 / bar_p1) and the block is reused for the second half once PV of the first has read
-//      it (bar_pfree: one tcgen05.commit per PV half).
+//   2. P_t goes to shared memory in two 64-token halves, each with its OWN 16 KiB block, handed to the MMA warp as soon
+//      as it is written (bar_p0 / bar_p1).  A block is rewritten one whole KV tile later, when the PV half that read it
+//      (bar_pfree0 / bar_pfree1: one tcgen05.commit per PV half) is long done; with one block for both halves the
+//      softmax warps spent 16 % of their time waiting for the first PV half, which the in-order MMA pipe runs behind
+//      the next tile's QK (profiles/r2_s7_*).
 // MASK is a template parameter so the (rare) masked tiles do not tax the common path with predicated-off
 // instructions (nvcc if-converts a runtime `if` around the element loop).
 template <bool MASK>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const float scale_log2,
                                              float& m_used, float& l_run, const uint32_t p_row, const int r7, const uint32_t bar_sfree,
-                                             const uint32_t bar_p0, const uint32_t bar_p1, const uint32_t bar_pfree, int& pfc) {
+                                             const uint32_t bar_p0, const uint32_t bar_p1, const uint32_t bar_pfree0, const int pn) {
   uint32_t sv[4][32];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
@@ -129,52 +199,98 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   const bool rescale = __any_sync(0xffffffffu, grow);   // warp-uniform, rare (lazy threshold 2^8)
   const float neg_m = -m_used;
   float s0 = 0.f, s1 = 0.f;
-  // Before the first P chunk of a half is stored: the PV MMAs that read the block's previous contents are done
-  // (PV half #(pfc-1), counted over the whole kernel), and -- first half only -- O_t carries the scale P assumes.
+  // Before a half is stored: the PV MMAs that read the block's previous contents (same half of this group's previous
+  // P tile, #pn-1 counted over the whole kernel) are done, and -- first half only -- O_t carries the scale P assumes.
   auto before_half = [&](int half) {
-    if (pfc > 0) mbar_wait(bar_pfree, (pfc - 1) & 1);
-    ++pfc;
-    if (half == 0 && rescale) rescale_o(tO, alpha);
+    if (pn > 0) mbar_wait(bar_pfree0 + 8u * half, (pn - 1) & 1);
+    if (half == 0 && rescale) {
+      if (pn > 0) mbar_wait(bar_pfree0 + 8u, (pn - 1) & 1);   // O_t is rewritten: BOTH PV halves of the previous tile are done
+      tc_fence_after();
+      rescale_o(tO, alpha);
+    }
   };
   auto after_half = [&](int half) {
     fence_proxy_async_smem();              // generic-proxy stores -> visible to the tensor core's async-proxy reads
     mbar_arrive(half ? bar_p1 : bar_p0);
   };
   if constexpr (!MASK) {
-    // Unmasked tiles (the common case): explicit software pipeline over the 128 elements.  The scale FMA runs
-    // kAhead elements ahead of its MUFU.EX2, the row-sum add and the bf16 pack kAhead elements behind it, so every
-    // MUFU (one per 8 clk per scheduler) has independent FMA-pipe work beside it.
-    constexpr int kAhead = 12;
-    uint32_t pw[32];     // the packed P of one 64-token half: stored in one go at the END of the half, ~1000 clk after the
-                         // previous half was handed over, so the bar_pfree wait in before_half() has long been satisfied
-                         // (storing chunk by chunk put that wait 8 elements behind the hand-over: the softmax warps spent
-                         // 38 % of their samples on it, profiles/r2_s5_*)
+    // Unmasked tiles (the common case): explicit software pipeline over the 64 element PAIRS of the row, in groups of
+    // 4 pairs (= one 16-byte chunk of P).  Per group, three instruction queues are interleaved one to one:
+    //   M  MUFU.EX2 of the group's pairs that take the hardware exponential
+    //   X  the FMA-pipe exponential of kEmuPairs of the 4 pairs (Cody-Waite split + degree-3 polynomial, packed f32x2)
+    //   F  the scale FFMA2 of the NEXT group, and row sum (FADD2) + bf16 pack + STS.128 of the PREVIOUS group
+    // MUFU (16 lanes/clk/SM) is as long as the MMAs of a KV tile (2048 clk per 2 x 128 rows x 128 tokens): with all
+    // exponentials on it the tensor pipe cannot pass ~50 % (profiles/r2_s7_*: XU pipe 48 % == tensor pipe 48 %).
+    const uint64_t sc2 = pack2(__float_as_uint(scale_log2), __float_as_uint(scale_log2));
+    const uint64_t nm2 = pack2(__float_as_uint(neg_m), __float_as_uint(neg_m));
+    uint64_t sp[64];
 #pragma unroll
-    for (int e = 0; e < kAhead; ++e)
-      sv[e >> 5][e & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[e >> 5][e & 31]), scale_log2, neg_m));
+    for (int q = 0; q < 64; ++q) sp[q] = pack2(sv[q >> 4][(2 * q) & 31], sv[q >> 4][(2 * q + 1) & 31]);
+    uint64_t acc_a = pack2(0u, 0u), acc_b = pack2(0u, 0u);
 #pragma unroll
-    for (int e = 0; e < 128 + kAhead; ++e) {
-      if ((e & 7) == 0) sched_fence();
-      if (e < 128) sv[e >> 5][e & 31] = __float_as_uint(exp2_ordered(__uint_as_float(sv[e >> 5][e & 31])));
-      if (e + kAhead < 128) {
-        const int f = e + kAhead;
-        sv[f >> 5][f & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[f >> 5][f & 31]), scale_log2, neg_m));
-      }
-      if (e >= kAhead) {
-        const int d = e - kAhead;
-        if (d & 1) {
-          s1 = add_ordered(s1, __uint_as_float(sv[d >> 5][d & 31]));
-          pw[(d >> 1) & 31] = pack_bf16x2_ordered(__uint_as_float(sv[(d - 1) >> 5][(d - 1) & 31]), __uint_as_float(sv[d >> 5][d & 31]));
-          if ((d & 63) == 63) {
-            before_half(d >> 6);
+    for (int q = 0; q < 4; ++q) sp[q] = fma2_ordered(sp[q], sc2, nm2);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) p_store_chunk(p_row, r7, c, pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
-            after_half(d >> 6);
+    for (int g = 0; g <= 16; ++g) {
+      sched_fence();
+      uint64_t et[2], ef[2], ep[2];
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 18; ++k) {
+        // ---- M: hardware exponentials -----------------------------------------------------------------------
+        if (g < 16 && k < 2 * (4 - kEmuPairs)) {
+          const int q = 4 * g + (kEmuPairs == 2 ? (k >> 1) * 2 : (k >> 1));
+          uint32_t lo, hi;
+          unpack2(sp[q], lo, hi);
+          if (k & 1) hi = __float_as_uint(exp2_ordered(__uint_as_float(hi)));
+          else lo = __float_as_uint(exp2_ordered(__uint_as_float(lo)));
+          sp[q] = pack2(lo, hi);
+        }
+        // ---- X: FMA-pipe exponentials -------------------------------------------------------------------------
+        if (g < 16 && k < 9 * kEmuPairs) {
+          const int i = kEmuPairs == 2 ? (k & 1) : 0;                   // which emulated pair of the group
+          const int step = kEmuPairs == 2 ? (k >> 1) : k;
+          const int q = 4 * g + (kEmuPairs == 2 ? 2 * i + 1 : 3);
+          if (step == 0) sp[q] = clamp_lo_ordered(sp[q]);
+          else if (step == 1) sp[q] = clamp_hi_ordered(sp[q]);
+          else if (step == 2) et[i] = add2_rm_ordered(sp[q], kMagic2);                   // low mantissa bits = floor(y)
+          else if (step == 3) ef[i] = sub2_ordered(et[i], kMagic2);                      // floor(y)
+          else if (step == 4) ef[i] = sub2_ordered(sp[q], ef[i]);                        // y - floor(y) in [0, 1)
+          else if (step == 5) ep[i] = fma2_ordered(kPolyC3, ef[i], kPolyC2);
+          else if (step == 6) ep[i] = fma2_ordered(ep[i], ef[i], kPolyC1);
+          else if (step == 7) ep[i] = fma2_ordered(ep[i], ef[i], kPolyC0);
+          else sp[q] = exp2_combine_ordered(ep[i], et[i]);                               // 2^floor(y) into the exponent
+        }
+        // ---- F: scale the next group, sum + pack + store the previous one ----------------------------------------
+        if (k < 4) {
+          if (g + 1 < 16) sp[4 * (g + 1) + k] = fma2_ordered(sp[4 * (g + 1) + k], sc2, nm2);
+        } else if (k < 8) {
+          if (g >= 1) {
+            const int q = 4 * (g - 1) + (k - 4);
+            if (k & 1) acc_b = add2_ordered(acc_b, sp[q]);
+            else acc_a = add2_ordered(acc_a, sp[q]);
           }
-        } else {
-          s0 = add_ordered(s0, __uint_as_float(sv[d >> 5][d & 31]));
+        } else if (k < 12) {
+          if (g >= 1) {
+            uint32_t lo, hi;
+            unpack2(sp[4 * (g - 1) + (k - 8)], lo, hi);
+            w[k - 8] = pack_bf16x2_ordered(__uint_as_float(lo), __uint_as_float(hi));
+          }
+        } else if (k == 12) {
+          if (g >= 1) {
+            const int c = (g - 1) & 7, half = (g - 1) >> 3;
+            if (c == 0) before_half(half);
+            p_store_chunk(p_row + (uint32_t)half * kBlkBytes, r7, c, w[0], w[1], w[2], w[3]);
+            if (c == 7) after_half(half);
+          }
         }
       }
+    }
+    {
+      const uint64_t acc = add2_ordered(acc_a, acc_b);
+      uint32_t lo, hi;
+      unpack2(acc, lo, hi);
+      s0 = __uint_as_float(lo);
+      s1 = __uint_as_float(hi);
     }
   } else {
 #pragma unroll
@@ -191,7 +307,8 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       }
       before_half(half);
 #pragma unroll
-      for (int c = 0; c < 8; ++c) p_store_chunk(p_row, r7, c, pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
+      for (int c = 0; c < 8; ++c)
+        p_store_chunk(p_row + (uint32_t)half * kBlkBytes, r7, c, pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
       after_half(half);
     }
   }
@@ -224,9 +341,13 @@ constexpr int kPlanThreads = 1024;
 constexpr int kPlanBuckets = 1024;
 constexpr int kWorkHeaderInts = 16;     // [0] work counter, [1] number of (sequence, tile) pairs
 // Dynamic shared memory: 2 Q tiles + 4-slot K/V ring + one 32 KiB tile the softmax warps stage output rows in.
-constexpr int kWsOffP = kWsOffRing + kRing * kTileBytes2;       // P_0, P_1: one [128 x 64] bf16 block (16 KiB) per query tile
+constexpr int kWsOffP = kWsOffRing + kRing * kTileBytes2;       // P_0, P_1: two [128 x 64] bf16 blocks (2 x 16 KiB) per query tile
 constexpr int kWsOffStage = kWsOffP;                            // the epilogue stages output rows in the (then idle) P blocks
-constexpr int kPersistSmem = kWsOffP + 2 * kBlkBytes + 1024;
+constexpr int kPersistSmem = kWsOffP + 2 * kTileBytes2 + 1024;
+
+// Ring order of one item's 2J tile fills == the order the MMA warp releases them:  K0 K1 V0 K2 V1 ... K(J-1) V(J-2) V(J-1)
+__device__ __forceinline__ int ring_seq_k(int j) { return j == 0 ? 0 : 2 * j - 1; }
+__device__ __forceinline__ int ring_seq_v(int j, int J) { return j + 1 < J ? 2 * j + 2 : 2 * J - 1; }
 
 struct ItemDesc {
   int s, kvh, j0, Lq, Lkv, q0, page0, valid;
@@ -304,7 +425,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
                                                                                const __grid_constant__ CUtensorMap tm_v) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing + 4];
+  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing + 6];
   __shared__ __align__(16) ItemDesc s_items[kItemRing];
   __shared__ __align__(16) int s_slots[2][2][2][32];   // cp.async producers: [tile parity][warp][row parity][i]
 
@@ -325,7 +446,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   auto bar_ifull = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + slot); };
   auto bar_iempty = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + kItemRing + slot); };
   auto bar_sfree = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + t); };      // S_t is in registers
-  auto bar_pfree = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + 2 + t); };  // a PV half has read P_t
+  auto bar_pfree = [&](int t, int half) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + 2 + 2 * t + half); };  // PV has read that half of P_t
   constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 TMA warps (lane 0 of each arrives)
 
   if (tid == 0) {
@@ -341,7 +462,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_init(bar_p(t, 1), 128);
       mbar_init(bar_o(t), 1);
       mbar_init(bar_sfree(t), 128);
-      mbar_init(bar_pfree(t), 1);
+      mbar_init(bar_pfree(t, 0), 1);
+      mbar_init(bar_pfree(t, 1), 1);
     }
     for (int i = 0; i < kItemRing; ++i) {
       mbar_init(bar_ifull(i), 1);
@@ -427,7 +549,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
     int qn = 0;
     if (tma_kv) {
       const CUtensorMap* tm = lw ? &tm_v : &tm_k;
-      int fill = lw;                                   // running ring-fill index of this warp's next tile
+      int gbase = 0;                                   // ring fills of all previous items
       for (int it = 0;; ++it) {
         const ItemDesc d = take_item(it);
         if (!d.valid) break;
@@ -455,7 +577,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         }
         ++qn;
         const int col = d.kvh * kTD;
-        for (int tile = 0; tile < g.J; ++tile, fill += 2) {
+        for (int tile = 0; tile < g.J; ++tile) {
+          const int fill = gbase + (lw ? ring_seq_v(tile, g.J) : ring_seq_k(tile));
           const int slot = fill % kRing, use = fill / kRing;
           if (tile + 1 < g.J) ldg_slots(tile + 1, sn);      // in flight behind this tile's issue loop
           mbar_wait(bar_empty(slot), (use & 1) ^ 1);
@@ -468,6 +591,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
 #pragma unroll
           for (int i = 0; i < 4; ++i) sl[i] = sn[i];
         }
+        gbase += 2 * g.J;
       }
     } else {
       const int lt = tid - 9 * 32;                    // 0..63
@@ -501,7 +625,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           mbar_wait(bar, parity);
         }
       };
-      int kc = 0, vc = 0;                              // K / V tiles filled so far (whole kernel)
+      int gbase = 0;                                   // ring fills of all previous items
       for (int it = 0;; ++it) {
         wait_or_flush(bar_ifull(it % kItemRing), (it / kItemRing) & 1);
         const ItemDesc d = take_item(it);
@@ -541,7 +665,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         }
         const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)d.kvh * kTD + gc * 8);
         const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)d.kvh * kTD + gc * 8);
-        auto fill_tile = [&](const char* base, int tile, int slot, int use) {
+        auto fill_tile = [&](const char* base, int tile, int fill) {
+          const int slot = fill % kRing, use = fill / kRing;
           __syncwarp();
           int sl[32];
           const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
@@ -566,21 +691,17 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           }
           rotate(bar_full(slot));
         };
-        fill_tile(kbase, 0, 2 * (kc & 1), kc >> 1);
-        ++kc;
+        fill_tile(kbase, 0, gbase);
         for (int j = 0; j < g.J; ++j) {
           if (j + 2 < g.J) ldg_pages(j + 2);               // consumed after V(j) has been issued
-          if (j + 1 < g.J) {
-            fill_tile(kbase, j + 1, 2 * (kc & 1), kc >> 1);
-            ++kc;
-          }
-          fill_tile(vbase, j, 2 * (vc & 1) + 1, vc >> 1);
-          ++vc;
+          if (j + 1 < g.J) fill_tile(kbase, j + 1, gbase + ring_seq_k(j + 1));
+          fill_tile(vbase, j, gbase + ring_seq_v(j, g.J));
           if (j + 2 < g.J) {
             __syncwarp();                                  // V(j) has read tile j's slot ids: its parity is free
             put_slots(j + 2);
           }
         }
+        gbase += 2 * g.J;
       }
       flush();
     }
@@ -619,12 +740,12 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
     // f = running ring-fill index of the V tile; half = 64-token half of the tile (4 K steps of 16 tokens)
     auto issue_pv_half = [&](int t, int f, int half, bool acc) {
       const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4)) + (uint64_t)(half * 4 * (2048 >> 4));
-      const uint64_t pd = pdesc0 + (uint64_t)(t * (kBlkBytes >> 4));
+      const uint64_t pd = pdesc0 + (uint64_t)((2 * t + half) * (kBlkBytes >> 4));
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks)
         umma_ss_elect(tmem + 2 * kTN + t * kTD, pd + (uint64_t)(ks * (32 >> 4)), vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
                       (acc || ks > 0));
-      umma_commit_elect(bar_pfree(t));
+      umma_commit_elect(bar_pfree(t, half));
     };
     int fillc = 0, qn = 0;
     for (int it = 0;; ++it) {
@@ -641,7 +762,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       umma_commit_elect(bar_empty(base % kRing));                        // K(0) free once both QK(0) are done
       if (g.J == 1) umma_commit_elect(bar_qfree);                        // last QK of the item: Q may be refilled
       for (int j = 0; j < g.J; ++j) {
-        const int fv = base + 2 * j + 1, fk = base + 2 * j + 2;
+        const int fv = base + ring_seq_v(j, g.J), fk = base + ring_seq_k(j + 1);
         if (j + 1 < g.J) {                                               // scores of the NEXT tile, under this tile's softmax
           mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);             // K(j+1)
           tc_fence_after();
@@ -679,9 +800,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem + lane_base + t * kTN;
     const uint32_t tO = tmem + lane_base + 2 * kTN + t * kTD;
-    const uint32_t p_row = smem + kWsOffP + (uint32_t)t * kBlkBytes + (uint32_t)r * 128u;   // my row of the P_t block
-    int sc = 0, oc = 0;
-    int pfc = 0;                                      // P halves written so far (whole kernel)
+    const uint32_t p_row = smem + kWsOffP + (uint32_t)t * kTileBytes2 + (uint32_t)r * 128u;   // my row of P_t's first block
+    int sc = 0, oc = 0;                               // sc = S / P tiles of this group so far (whole kernel)
     for (int it = 0;; ++it) {
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
@@ -701,10 +821,10 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         if (need_mask) {
           const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
           softmax_tile<true>(tS, tO, nvalid, p.scale_log2, m_used, l_run, p_row, r & 7, bar_sfree(t), bar_p(t, 0), bar_p(t, 1),
-                             bar_pfree(t), pfc);
+                             bar_pfree(t, 0), sc);
         } else {
           softmax_tile<false>(tS, tO, kTN, p.scale_log2, m_used, l_run, p_row, r & 7, bar_sfree(t), bar_p(t, 0), bar_p(t, 1),
-                              bar_pfree(t), pfc);
+                              bar_pfree(t, 0), sc);
         }
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
@@ -720,7 +840,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       // each and the 8 softmax warps spent ~4000 LSU wavefront-cycles per item in the epilogue (14 % of their
       // time on bench-shaped prompts).  Staging area, 4 KiB per warp (32 rows x 64 columns bf16, 16-byte pieces
       // XOR-swizzled by row): this warp's own 32 rows of the P_t block, idle once bar_o says every PV_t has read it.
-      const uint32_t stage = smem + kWsOffStage + (uint32_t)warp * 4096u;
+      const uint32_t stage = smem + kWsOffStage + (uint32_t)t * kTileBytes2 + (uint32_t)(warp & 3) * 4096u;
       const int rows_ok = tokst << log2_g;
       const int rsub = lane >> 3, piece = lane & 7;
       if (!has && r < rows_ok) {
