@@ -21,7 +21,7 @@
 #include "tma.cuh"
 
 #ifndef B200_PREFILL_EMU_PAIRS
-#define B200_PREFILL_EMU_PAIRS 1
+#define B200_PREFILL_EMU_PAIRS 0
 #endif
 
 namespace b200 {
