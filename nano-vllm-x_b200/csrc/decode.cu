@@ -52,6 +52,8 @@ constexpr int kMinTilesPerStream = 2;  // do not split finer than 32 tokens per 
 constexpr int kMaxSmemSeqs = 4096;     // batches up to this size keep their tile prefix in shared memory
 constexpr int kMinDynUnit = 4;         // dynamic chunks are >= 4 tiles (> the producer's 3-tile lookahead)
 constexpr int kDynChunksPerStream = 6; // 1 of 8u + 1 of 4u + 4 of u tiles per stream
+constexpr int kCtrlBytes = 64;         // control block at the start of the workspace (survives between calls)
+constexpr unsigned long long kCtrlMagic = 0xB200DEC0ull << 32;   // high word of a control word that was initialised
 
 struct DecodeParams {
   const __nv_bfloat16* q;
@@ -65,7 +67,7 @@ struct DecodeParams {
   float* part_lse;    // [G*subs+B][Hq]
   int32_t* seg_first; // [B]
   int32_t* seg_last;  // [B]
-  int32_t* counter;   // chunk counter (zeroed by the launcher) or nullptr: static split only
+  unsigned long long* counter;   // control word {magic : 32, chunks claimed : 32} or nullptr: static split only
   int64_t q_row_stride, out_row_stride, kv_slot_stride;
   int B, Hq, Hkv, group, log2_ps;
   int heads_per_cta;  // KV heads handled by one CTA (<= 8)
@@ -123,7 +125,11 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
       return cb < total;
     }
     int c = 0;
-    if (lane == 0) c = atomicAdd(p.counter, 1);
+    if (lane == 0) {
+      const unsigned long long v = atomicAdd(p.counter, 1ull);
+      if ((v >> 32) != (kCtrlMagic >> 32)) __trap();   // workspace never went through b200_decode_workspace_init
+      c = (int)(unsigned)v;
+    }
     c = __shfl_sync(0xffffffffu, c, 0);
     if (c < n_streams) {
       cb = c * 8 * unit;
@@ -437,50 +443,74 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   cp_async_wait<0>();
 }
 
-// Merge pass: one CTA per (sequence, query head); 4 warps split the partial list, a lane owns 4 output
-// dims (float4 loads: one coalesced 512-byte row per partial per warp), warps combine through smem.
-__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
-  const int s = blockIdx.x, hq = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// Merge pass: one CTA per (sequence, query head), 8 warps.  The log-sum-exps of the partial list are read lane-parallel
+// (one round trip for up to 256 partials), their maximum and the weights go through shared memory, then the warps split
+// the list, a lane owns 4 output dims (float4 loads: one coalesced 512-byte row per partial per warp) with 8 loads in
+// flight per lane, and combine through shared memory.  With the dynamic split a long sequence owns ~100 partials:
+// the 4-warp two-pass version spent ~14 dependent round trips on them.
+constexpr int kMergeThreads = 256;
+constexpr int kMergeWarps = kMergeThreads / 32;
+constexpr int kMergeMaxW = 1024;      // weights kept in shared memory; longer lists recompute them from the lse
+__global__ void __launch_bounds__(kMergeThreads) decode_merge_kernel(const DecodeParams p) {
+  const int s = blockIdx.x, hq = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD;
+  __shared__ float s_red[kMergeWarps];
+  __shared__ float s_w[kMergeMaxW];
+  __shared__ float4 s_acc[kMergeWarps][32];
   griddep_wait();                     // launched with PDL: partials / segment maps come from decode_kernel
+  // the chunk counter goes back to zero for the next launch (every claim of this launch has been made)
+  if (p.counter != nullptr && s == 0 && hq == 0 && tid == 0) *p.counter = kCtrlMagic;
   const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
   if (L == 0) {
-    dst[threadIdx.x] = __float2bfloat16(0.f);
+    if (tid < kD) dst[tid] = __float2bfloat16(0.f);
     return;
   }
   const int first = p.seg_first[s], last = p.seg_last[s];
   if (first == last) return;  // one segment: written directly by the streaming kernel
   const int n = last - first + 1;
   const float* lse = p.part_lse + (int64_t)first * p.Hq + hq;
+  float mx = -INFINITY;
+  for (int i = tid; i < n; i += kMergeThreads) mx = fmaxf(mx, lse[(int64_t)i * p.Hq]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) s_red[warp] = mx;
+  __syncthreads();
+  mx = s_red[0];
+#pragma unroll
+  for (int w = 1; w < kMergeWarps; ++w) mx = fmaxf(mx, s_red[w]);
+  for (int i = tid; i < min(n, kMergeMaxW); i += kMergeThreads) {
+    const float l = lse[(int64_t)i * p.Hq];           // L1 hit: read a moment ago
+    s_w[i] = l == -INFINITY ? 0.f : fast_exp2(l - mx);
+  }
+  __syncthreads();
   const float4* po = reinterpret_cast<const float4*>(p.part_o + ((int64_t)first * p.Hq + hq) * kD) + lane;
   const int64_t po_stride = (int64_t)p.Hq * kD / 4;
-  __shared__ float s_m[4], s_w[4];
-  __shared__ float4 s_acc[4][32];
-  float mx = -INFINITY;
-  for (int i = warp; i < n; i += 4) mx = fmaxf(mx, lse[(int64_t)i * p.Hq]);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   float wsum = 0.f;
-#pragma unroll 4
-  for (int i = warp; i < n; i += 4) {
-    const float l = lse[(int64_t)i * p.Hq];
-    const float w = l == -INFINITY ? 0.f : fast_exp2(l - mx);
+#pragma unroll 8
+  for (int i = warp; i < n; i += kMergeWarps) {
+    float w;
+    if (i < kMergeMaxW) {
+      w = s_w[i];
+    } else {
+      const float l = lse[(int64_t)i * p.Hq];
+      w = l == -INFINITY ? 0.f : fast_exp2(l - mx);
+    }
     const float4 v = po[(int64_t)i * po_stride];
     wsum += w;
     acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z; acc.w += w * v.w;
   }
-  if (lane == 0) { s_m[warp] = mx; s_w[warp] = wsum; }
+  if (lane == 0) s_red[warp] = wsum;   // (every thread has read the maxima: they were consumed before the last barrier)
   s_acc[warp][lane] = acc;
   __syncthreads();
   if (warp == 0) {
-    const float M = fmaxf(fmaxf(s_m[0], s_m[1]), fmaxf(s_m[2], s_m[3]));
     float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
     float W = 0.f;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) {
-      const float f = s_m[w] == -INFINITY ? 0.f : fast_exp2(s_m[w] - M);
+    for (int w = 0; w < kMergeWarps; ++w) {
       const float4 a = s_acc[w][lane];
-      W += f * s_w[w];
-      r.x += f * a.x; r.y += f * a.y; r.z += f * a.z; r.w += f * a.w;
+      W += s_red[w];
+      r.x += a.x; r.y += a.y; r.z += a.z; r.w += a.w;
     }
     const float inv = W > 0.f ? 1.f / W : 0.f;
     uint2 o2;
@@ -488,6 +518,10 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p)
     o2.y = pack_bf16x2(r.z * inv, r.w * inv);
     *reinterpret_cast<uint2*>(dst + lane * 4) = o2;
   }
+}
+
+__global__ void decode_ws_init_kernel(unsigned long long* ctrl) {
+  if (threadIdx.x == 0) ctrl[0] = kCtrlMagic;
 }
 
 static int ilog2_exact_d(int x) {
@@ -531,8 +565,16 @@ extern "C" size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv
   size_t bytes = parts * Hq * D * sizeof(float);       // part_o
   bytes += parts * Hq * sizeof(float);                 // part_lse
   bytes += 2 * (size_t)B * sizeof(int32_t);            // seg_first / seg_last
-  bytes += 64;                                         // chunk counter of the dynamic split
+  bytes += kCtrlBytes;                                 // control block (chunk counter of the dynamic split)
   return (bytes + 255) & ~(size_t)255;
+}
+
+extern "C" int b200_decode_workspace_init(void* workspace, size_t workspace_bytes, b200_stream_t stream) {
+  using namespace b200;
+  if (!workspace || workspace_bytes < (size_t)kCtrlBytes) return fail("b200_decode_workspace_init: workspace < %d bytes", kCtrlBytes);
+  if ((uintptr_t)workspace & 15) return fail("b200_decode_workspace_init: workspace must be 16-byte aligned");
+  decode_ws_init_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((unsigned long long*)workspace);
+  return check_launch("b200_decode_workspace_init");
 }
 
 extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
@@ -571,11 +613,11 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   p.last_page_len = last_page_len;
   p.out = (__nv_bfloat16*)out;
   const size_t parts = decode_parts(G, c, B);
-  p.part_o = (float*)workspace;
+  p.part_o = (float*)((char*)workspace + kCtrlBytes);
   p.part_lse = p.part_o + parts * Hq * D;
   p.seg_first = (int32_t*)(p.part_lse + parts * Hq);
   p.seg_last = p.seg_first + B;
-  p.counter = decode_dynamic(c) ? p.seg_last + B : nullptr;
+  p.counter = decode_dynamic(c) ? (unsigned long long*)workspace : nullptr;
   p.q_row_stride = q_row_stride;
   p.out_row_stride = out_row_stride;
   p.kv_slot_stride = kv_slot_stride;
@@ -588,13 +630,9 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   if (cudaError_t e = ensure_dyn_smem(decode_kernel, kDecodeSmem, attr_done); e != cudaSuccess)
     return fail("b200_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   cudaStream_t st = (cudaStream_t)stream;
-  if (p.counter) {   // graph-capturable memset node; the kernel decides on the device (from the total tile count) whether it claims
-    if (cudaError_t e = cudaMemsetAsync(p.counter, 0, sizeof(int32_t), st); e != cudaSuccess)
-      return fail("b200_decode: cudaMemsetAsync: %s", cudaGetErrorString(e));
-  }
   decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
   if (int rc = check_launch("b200_decode(stream)")) return rc;
-  cudaError_t e = launch_pdl(decode_merge_kernel, dim3(B, Hq), dim3(128), 0, st, p);
+  cudaError_t e = launch_pdl(decode_merge_kernel, dim3(B, Hq), dim3(kMergeThreads), 0, st, p);
   if (e != cudaSuccess) return fail("b200_decode(merge): %s", cudaGetErrorString(e));
   return check_launch("b200_decode(merge)");
 }

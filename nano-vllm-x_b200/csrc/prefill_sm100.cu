@@ -9,20 +9,22 @@
 //   softmax rows in registers (thread == row == TMEM lane: no shuffles), exp2 domain, fp32
 //   O[128 x 128d] += P[128 x 128tok] . V_tile      UMMA 128x128x16, A K-major (P, bf16 in smem),
 //                                                  B MN-major (V rows are [token][d])
-// K/V tiles (128 tokens) are gathered through the page table with 16-byte cp.async into the
-// canonical SWIZZLE_128B layout (two [128 x 64] blocks of 128-byte rows, chunk ^= row & 7) — the
-// same bytes TMA would produce, but page_size 1 needs a per-row gather TMA tiles cannot express.
-// Double-buffered: tile t+1 streams in while tile t is on the tensor cores.
+// (Design "A".  Round 2 also built and measured design "B": S pulled into registers so that QK(j+1) runs under
+// softmax(j), P through shared memory, 3-slot ring -- git 7f19014.  Same box, 16 x 4096 Hq32/Hkv8: B 0.63 of bf16 peak
+// with 48 % tensor pipe, A 0.66, A with the packed-f32x2 softmax below 0.69 with 55 %: profiles/r2_s9_*, r2_s10_*.
+// B's SS-mode PV reads P and V from shared memory and saturates the tensor cores' shared-memory port; in both
+// designs the time goes into the ~700 instructions a softmax warp runs per 128 x 128 tile.)
+// Feed: Q always by TMA (tiled 3-D boxes); K/V tiles (128 tokens) by TMA tile::gather4 through the page table when
+// page_size >= 16 and by 16-byte cp.async gathers for the reference's token-granular pools (page_size 1: gather4
+// there is 64 single-row instructions per tile, each a ~90 clk elect loop on the uniform datapath: measured 0.69 ->
+// 0.46 of bf16 peak, profiles/r2_s4_*).  Either way the bytes land in the canonical SWIZZLE_128B layout (two
+// [128 x 64] blocks of 128-byte rows, chunk ^= row & 7).
 // O lives in TMEM across the KV loop; a row is rescaled in place (tcgen05.ld/st) only when its
 // running max moves.
 #include "common.cuh"
 #include "prefill_params.cuh"
 #include "sm100.cuh"
 #include "tma.cuh"
-
-#ifndef B200_PREFILL_EMU_PAIRS
-#define B200_PREFILL_EMU_PAIRS 0
-#endif
 
 namespace b200 {
 
@@ -40,8 +42,9 @@ constexpr int kTileBytes2 = 2 * kBlkBytes;     // a full [128 x 128] bf16 operan
 //   warps 0-3   softmax group 0  (rows   0..127 of the CTA's 256 packed rows; thread == row == TMEM lane)
 //   warps 4-7   softmax group 1  (rows 128..255)
 //   warp  8     MMA issuer (one thread): S_t = Q_t K^T, O_t += P_t V, t = 0,1
-//   warps 9-10  K/V/Q loaders: 16-byte cp.async gathers through the page table into a 4-slot ring
-//               of SWIZZLE_128B tiles (K0,V0,K1,V1,...), released by tcgen05.commit
+//   warps 9-10  producers: TMA for Q (and for K/V at page_size >= 16), cp.async gathers for K/V at page_size < 16,
+//               into a 4-slot ring of SWIZZLE_128B tiles (K slots 0/2, V slots 1/3), released by tcgen05.commit
+//   warp  11    scheduler of the persistent work list
 //
 // TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512).  P_t (bf16) is written by
 // tcgen05.st over the first 64 columns of S_t and consumed as the TMEM A operand of the PV MMA, so P
@@ -53,42 +56,18 @@ constexpr int kTileBytes2 = 2 * kBlkBytes;     // a full [128 x 128] bf16 operan
 // (exact: O and l carry the same stale scale until the final division).
 // =====================================================================================================
 constexpr int kWsThreads = 384;   // 3 warpgroups: softmax0, softmax1, {MMA, 2 loaders, 1 spare}
-constexpr int kRing = 3;                             // K(j+1), V(j) in use + one tile in flight; filled in consumption order
+constexpr int kRing = 4;
 constexpr int kWsOffQ = 0;                           // 2 x 32 KiB
 constexpr int kWsOffRing = 2 * kTileBytes2;          // kRing x 32 KiB
 constexpr float kLazyTau = 8.0f;
 
-// Rare path of the lazy rescale (a row max grew by more than 2^kLazyTau): O_t *= alpha in TMEM.  Kept out of line
-// so that its 32-register O chunk never competes with the 128 S values of the hot path for registers.
-__device__ __noinline__ void rescale_o(const uint32_t tO, const float alpha) {
-#pragma unroll 1
-  for (int c = 0; c < 4; ++c) {
-    uint32_t ov[32];
-    tmem_ld_32x32b_x32(tO + c * 32, ov);
-    tmem_wait_ld();
-#pragma unroll
-    for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
-    tmem_st_32x32b_x32(tO + c * 32, ov);
-  }
-  tmem_wait_st();
-  tc_fence_before();
-}
-
-// 8 P values (tokens 8c..8c+7 of a 64-token half) of this thread's row -> the SWIZZLE_128B K-major P block
-// (row r: 128 bytes at r*128, 16-byte chunk c at (c ^ (r & 7)) << 4): conflict-free STS.128, the layout the PV
-// MMA's A descriptor reads.
-__device__ __forceinline__ void p_store_chunk(const uint32_t p_row, const int r7, const int c, const uint32_t w0, const uint32_t w1,
-                                              const uint32_t w2, const uint32_t w3) {
-  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(p_row + (uint32_t)((c ^ r7) << 4)), "r"(w0), "r"(w1), "r"(w2), "r"(w3)
-               : "memory");
-}
-
-// ---- packed f32x2 helpers (FFMA2 / FADD2 on sm_100) and the FMA-pipe exponential --------------------------------
-// All arithmetic forms are `asm volatile`: together with bar.warp.sync fences they pin the instruction ORDER of the
-// softmax software pipeline (ptxas keeps volatile asm in program order); the mov.b64 pack / unpack forms are plain
-// register-pair aliases and cost no instruction.
-constexpr int kEmuPairs = B200_PREFILL_EMU_PAIRS;   // of every 4 element pairs, how many take the FMA-pipe exponential
-static_assert(kEmuPairs >= 0 && kEmuPairs <= 2, "B200_PREFILL_EMU_PAIRS must be 0, 1 or 2");
+// ---- packed f32x2 helpers (FFMA2 / FADD2 on sm_100).  The arithmetic forms are `asm volatile`: together with the
+// bar.warp.sync fences they pin the instruction ORDER of the softmax software pipeline; the mov.b64 pack / unpack forms
+// are plain register-pair aliases and cost no instruction.
+#ifndef B200_PREFILL_PACKED
+#define B200_PREFILL_PACKED 1
+#endif
+constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -107,77 +86,32 @@ __device__ __forceinline__ uint64_t add2_ordered(uint64_t a, uint64_t b) {
   asm volatile("add.rn.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
-__device__ __forceinline__ uint64_t add2_rm_ordered(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm volatile("add.rm.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ uint64_t sub2_ordered(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm volatile("sub.rn.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-// exp2 on the FMA pipe (the FlashAttention-4 scheme): y = n + f, n = floor(y) (add.rm against 1.5 * 2^23 leaves n in the
-// low mantissa bits), 2^f by a degree-3 polynomial on [0, 1) (max relative error 8.8e-5, far inside bf16's 2^-9; p(0) == 1
-// exactly, so the row maximum still maps to 1), then n is added into the exponent field.  y is clamped at -126 first (the
-// result of anything below is a denormal P that bf16 flushes anyway).
-#define B200_F2X(bits) ((uint64_t)(bits) | ((uint64_t)(bits) << 32))
-constexpr uint64_t kMagic2 = B200_F2X(0x4B400000u);   // 12582912.0f = 1.5 * 2^23
-constexpr uint64_t kPolyC0 = B200_F2X(0x3F800000u);   // 1.0
-constexpr uint64_t kPolyC1 = B200_F2X(0x3F31F519u);   // 0.695146143436431884765625
-constexpr uint64_t kPolyC2 = B200_F2X(0x3E6906A4u);   // 0.227564394474029541015625
-constexpr uint64_t kPolyC3 = B200_F2X(0x3D9DF09Du);   // 0.077119089663028717041015625
-__device__ __forceinline__ uint64_t clamp_lo_ordered(uint64_t v) {
-  uint64_t r;
-  asm volatile("{\n\t.reg .f32 a, b;\n\tmov.b64 {a, b}, %1;\n\tmax.f32 a, a, 0fC2FC0000;\n\tmov.b64 %0, {a, b};\n\t}\n" : "=l"(r) : "l"(v));
-  return r;
-}
-__device__ __forceinline__ uint64_t clamp_hi_ordered(uint64_t v) {
-  uint64_t r;
-  asm volatile("{\n\t.reg .f32 a, b;\n\tmov.b64 {a, b}, %1;\n\tmax.f32 b, b, 0fC2FC0000;\n\tmov.b64 %0, {a, b};\n\t}\n" : "=l"(r) : "l"(v));
-  return r;
-}
-__device__ __forceinline__ uint64_t exp2_combine_ordered(uint64_t p, uint64_t t) {
-  uint64_t r;
-  asm volatile(
-      "{\n\t.reg .b32 a, b, c, d;\n\tmov.b64 {a, b}, %1;\n\tmov.b64 {c, d}, %2;\n\t"
-      "shl.b32 c, c, 23;\n\tshl.b32 d, d, 23;\n\tadd.s32 a, a, c;\n\tadd.s32 b, b, d;\n\tmov.b64 %0, {a, b};\n\t}\n"
-      : "=l"(r)
-      : "l"(p), "l"(t));
-  return r;
-}
 
 // One softmax step of one row (thread) over a 128-column S tile held in TMEM.
-//   1. S_t -> registers, then bar_sfree: the MMA warp may overwrite S_t with QK_t(j+1) at once (it runs UNDER this
-//      tile's exponentials; S and P used to alias in TMEM, which chained softmax(j) -> PV(j) -> QK(j+1) -> softmax(j+1)
-//      and left the tensor pipe idle for half of every tile period: profiles/r1_s38_*).
-//   2. P_t goes to shared memory in two 64-token halves, each with its OWN 16 KiB block, handed to the MMA warp as soon
-//      as it is written (bar_p0 / bar_p1).  A block is rewritten one whole KV tile later, when the PV half that read it
-//      (bar_pfree0 / bar_pfree1: one tcgen05.commit per PV half) is long done; with one block for both halves the
-//      softmax warps spent 16 % of their time waiting for the first PV half, which the in-order MMA pipe runs behind
-//      the next tile's QK (profiles/r2_s7_*).
-// MASK is a template parameter so the (rare) masked tiles do not tax the common path with predicated-off
-// instructions (nvcc if-converts a runtime `if` around the element loop).
-template <bool MASK>
-__device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const float scale_log2,
-                                             float& m_used, float& l_run, const uint32_t p_row, const int r7, const uint32_t bar_sfree,
-                                             const uint32_t bar_p0, const uint32_t bar_p1, const uint32_t bar_pfree0, const int pn) {
-  uint32_t sv[4][32];
+// MASK is a template parameter so the (rare) masked tiles do not tax the common path with
+// predicated-off instructions (nvcc if-converts a runtime `if` around the element loop).
+template <bool MASK, int NCH = 4>
+__device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
+                                             const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
+                                             const uint32_t bar_p1) {
+  // NCH (masked tiles only, tile-uniform): number of 32-column chunks of S that hold any valid column of this
+  // query tile.  The MMA issuer trims QK to N = 32*NCH and PV to K = 32*NCH, so chunks >= NCH are neither
+  // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
+  static_assert(MASK || NCH == 4, "only masked tiles are trimmed");
+  uint32_t sv[NCH][32];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+  for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
   tmem_wait_ld();
-  tc_fence_before();
-  mbar_arrive(bar_sfree);                  // S_t is in registers: QK_t(j+1) may land
   if (MASK) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c)
+    for (int c = 0; c < NCH; ++c)
 #pragma unroll
       for (int e = 0; e < 32; ++e)
         if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
   }
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < NCH; ++c) {
 #pragma unroll
     for (int e = 0; e < 32; e += 4) {
       mx0 = fmaxf(mx0, __uint_as_float(sv[c][e]));
@@ -196,72 +130,41 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
     alpha = fast_exp2(m_used - mx);
     m_used = mx;
   }
-  const bool rescale = __any_sync(0xffffffffu, grow);   // warp-uniform, rare (lazy threshold 2^8)
+  const bool rescale = first_pv_done && __any_sync(0xffffffffu, grow);   // warp-uniform, rare (lazy threshold 2^8)
   const float neg_m = -m_used;
   float s0 = 0.f, s1 = 0.f;
-  // Before a half is stored: the PV MMAs that read the block's previous contents (same half of this group's previous
-  // P tile, #pn-1 counted over the whole kernel) are done, and -- first half only -- O_t carries the scale P assumes.
-  auto before_half = [&](int half) {
-    if (pn > 0) mbar_wait(bar_pfree0 + 8u * half, (pn - 1) & 1);
-    if (half == 0 && rescale) {
-      if (pn > 0) mbar_wait(bar_pfree0 + 8u, (pn - 1) & 1);   // O_t is rewritten: BOTH PV halves of the previous tile are done
-      tc_fence_after();
-      rescale_o(tO, alpha);
-    }
-  };
-  auto after_half = [&](int half) {
-    fence_proxy_async_smem();              // generic-proxy stores -> visible to the tensor core's async-proxy reads
-    mbar_arrive(half ? bar_p1 : bar_p0);
-  };
-  if constexpr (!MASK) {
-    // Unmasked tiles (the common case): explicit software pipeline over the 64 element PAIRS of the row, in groups of
-    // 4 pairs (= one 16-byte chunk of P).  Per group, three instruction queues are interleaved one to one:
-    //   M  MUFU.EX2 of the group's pairs that take the hardware exponential
-    //   X  the FMA-pipe exponential of kEmuPairs of the 4 pairs (Cody-Waite split + degree-3 polynomial, packed f32x2)
-    //   F  the scale FFMA2 of the NEXT group, and row sum (FADD2) + bf16 pack + STS.128 of the PREVIOUS group
-    // MUFU (16 lanes/clk/SM) is as long as the MMAs of a KV tile (2048 clk per 2 x 128 rows x 128 tokens): with all
-    // exponentials on it the tensor pipe cannot pass ~50 % (profiles/r2_s7_*: XU pipe 48 % == tensor pipe 48 %).
+  // The O rescale sits AFTER the exponentials in its own (rare) branch: with the rescale ahead of them ptxas
+  // hoists all 128 ex2 above it and spills 15 registers around the 32-register O chunk on the hot path.
+  if constexpr (!MASK && kPackedSoftmax) {
+    // Unmasked tiles (the common case): explicit software pipeline over the 64 element PAIRS of the row in groups of
+    // 4 pairs, with packed f32x2 arithmetic (FFMA2 / FADD2: half the FMA-pipe instructions of the scalar form).
+    // Per group two instruction queues are interleaved one to one:
+    //   M  the 8 MUFU.EX2 of the group
+    //   F  the scale FFMA2 of the NEXT group, then row sum (FADD2) and bf16 pack of the PREVIOUS group
+    // so every MUFU (one per 8 clk per scheduler) has independent FMA / ALU work beside it.
     const uint64_t sc2 = pack2(__float_as_uint(scale_log2), __float_as_uint(scale_log2));
     const uint64_t nm2 = pack2(__float_as_uint(neg_m), __float_as_uint(neg_m));
     uint64_t sp[64];
 #pragma unroll
     for (int q = 0; q < 64; ++q) sp[q] = pack2(sv[q >> 4][(2 * q) & 31], sv[q >> 4][(2 * q + 1) & 31]);
     uint64_t acc_a = pack2(0u, 0u), acc_b = pack2(0u, 0u);
+    uint32_t pw[16];       // packed P of one 32-column chunk
 #pragma unroll
     for (int q = 0; q < 4; ++q) sp[q] = fma2_ordered(sp[q], sc2, nm2);
 #pragma unroll
     for (int g = 0; g <= 16; ++g) {
       sched_fence();
-      uint64_t et[2], ef[2], ep[2];
-      uint32_t w[4];
 #pragma unroll
-      for (int k = 0; k < 18; ++k) {
-        // ---- M: hardware exponentials -----------------------------------------------------------------------
-        if (g < 16 && k < 2 * (4 - kEmuPairs)) {
-          const int q = 4 * g + (kEmuPairs == 2 ? (k >> 1) * 2 : (k >> 1));
+      for (int k = 0; k < 12; ++k) {
+        if (g < 16 && k < 8) {                                           // ---- M
+          const int q = 4 * g + (k >> 1);
           uint32_t lo, hi;
           unpack2(sp[q], lo, hi);
           if (k & 1) hi = __float_as_uint(exp2_ordered(__uint_as_float(hi)));
           else lo = __float_as_uint(exp2_ordered(__uint_as_float(lo)));
           sp[q] = pack2(lo, hi);
         }
-        // ---- X: FMA-pipe exponentials -------------------------------------------------------------------------
-        if (g < 16 && k < 9 * kEmuPairs) {
-          const int i = kEmuPairs == 2 ? (k & 1) : 0;                   // which emulated pair of the group
-          const int step = kEmuPairs == 2 ? (k >> 1) : k;
-          const int q = 4 * g + (kEmuPairs == 2 ? 2 * i + 1 : 3);
-          if (step == 0) sp[q] = clamp_lo_ordered(sp[q]);
-          else if (step == 1) sp[q] = clamp_hi_ordered(sp[q]);
-          else if (step == 2) et[i] = add2_rm_ordered(sp[q], kMagic2);                   // low mantissa bits = floor(y)
-          else if (step == 3) ef[i] = sub2_ordered(et[i], kMagic2);                      // floor(y)
-          else if (step == 4) ef[i] = sub2_ordered(sp[q], ef[i]);                        // y - floor(y) in [0, 1)
-          else if (step == 5) ep[i] = fma2_ordered(kPolyC3, ef[i], kPolyC2);
-          else if (step == 6) ep[i] = fma2_ordered(ep[i], ef[i], kPolyC1);
-          else if (step == 7) ep[i] = fma2_ordered(ep[i], ef[i], kPolyC0);
-          else sp[q] = exp2_combine_ordered(ep[i], et[i]);                               // 2^floor(y) into the exponent
-        }
-        // ---- F: scale the next group, sum + pack + store the previous one ----------------------------------------
-        if (k < 4) {
+        if (k < 4) {                                                     // ---- F
           if (g + 1 < 16) sp[4 * (g + 1) + k] = fma2_ordered(sp[4 * (g + 1) + k], sc2, nm2);
         } else if (k < 8) {
           if (g >= 1) {
@@ -269,51 +172,105 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
             if (k & 1) acc_b = add2_ordered(acc_b, sp[q]);
             else acc_a = add2_ordered(acc_a, sp[q]);
           }
-        } else if (k < 12) {
-          if (g >= 1) {
-            uint32_t lo, hi;
-            unpack2(sp[4 * (g - 1) + (k - 8)], lo, hi);
-            w[k - 8] = pack_bf16x2_ordered(__uint_as_float(lo), __uint_as_float(hi));
-          }
-        } else if (k == 12) {
-          if (g >= 1) {
-            const int c = (g - 1) & 7, half = (g - 1) >> 3;
-            if (c == 0) before_half(half);
-            p_store_chunk(p_row + (uint32_t)half * kBlkBytes, r7, c, w[0], w[1], w[2], w[3]);
-            if (c == 7) after_half(half);
-          }
+        } else if (g >= 1) {
+          const int q = 4 * (g - 1) + (k - 8);
+          uint32_t lo, hi;
+          unpack2(sp[q], lo, hi);
+          pw[q & 15] = pack_bf16x2_ordered(__uint_as_float(lo), __uint_as_float(hi));
+        }
+      }
+      if (g >= 1 && ((g - 1) & 3) == 3) {
+        const int c = (g - 1) >> 2;
+        tmem_st_32x32b_x16(tS + c * 16, pw);          // P: packed bf16x2 over S
+        if (!rescale && (c == 1 || c == 3)) {         // hand P over in two halves: PV starts on the first
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(c == 1 ? bar_p0 : bar_p1);
         }
       }
     }
     {
-      const uint64_t acc = add2_ordered(acc_a, acc_b);
       uint32_t lo, hi;
-      unpack2(acc, lo, hi);
+      unpack2(add2_ordered(acc_a, acc_b), lo, hi);
       s0 = __uint_as_float(lo);
       s1 = __uint_as_float(hi);
     }
+  } else if constexpr (!MASK) {
+    // Unmasked tiles (the common case): explicit software pipeline over the 128 elements.  The scale FMA runs
+    // kAhead elements ahead of its MUFU.EX2, the row-sum add and the bf16 pack kAhead elements behind it, so every
+    // MUFU (one per 8 clk per scheduler) has independent FMA-pipe work beside it.
+    constexpr int kAhead = 12;
+    uint32_t pw[64];
+#pragma unroll
+    for (int e = 0; e < kAhead; ++e)
+      sv[e >> 5][e & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[e >> 5][e & 31]), scale_log2, neg_m));
+#pragma unroll
+    for (int e = 0; e < 128 + kAhead; ++e) {
+      if ((e & 7) == 0) sched_fence();
+      if (e < 128) sv[e >> 5][e & 31] = __float_as_uint(exp2_ordered(__uint_as_float(sv[e >> 5][e & 31])));
+      if (e + kAhead < 128) {
+        const int f = e + kAhead;
+        sv[f >> 5][f & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[f >> 5][f & 31]), scale_log2, neg_m));
+      }
+      if (e >= kAhead) {
+        const int d = e - kAhead;
+        if (d & 1) {
+          s1 = add_ordered(s1, __uint_as_float(sv[d >> 5][d & 31]));
+          pw[d >> 1] = pack_bf16x2_ordered(__uint_as_float(sv[(d - 1) >> 5][(d - 1) & 31]), __uint_as_float(sv[d >> 5][d & 31]));
+          if ((d & 31) == 31) {
+            const int c = d >> 5;
+            tmem_st_32x32b_x16(tS + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&pw[c * 16]));   // P: packed bf16x2 over S
+            if (!rescale && (c == 1 || c == 3)) {     // hand P over in two halves: PV starts on the first
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(c == 1 ? bar_p0 : bar_p1);
+            }
+          }
+        } else {
+          s0 = add_ordered(s0, __uint_as_float(sv[d >> 5][d & 31]));
+        }
+      }
+    }
   } else {
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      uint32_t pw[32];
+  for (int c = 0; c < NCH; ++c) {
+    uint32_t pw[16];
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        const int c = half * 2 + (e >> 4), k = e & 15;
-        const float a = exp2_fma(__uint_as_float(sv[c][2 * k]), scale_log2, neg_m);
-        const float b = exp2_fma(__uint_as_float(sv[c][2 * k + 1]), scale_log2, neg_m);
-        s0 += a;
-        s1 += b;
-        pw[e] = pack_bf16x2(a, b);
-      }
-      before_half(half);
-#pragma unroll
-      for (int c = 0; c < 8; ++c)
-        p_store_chunk(p_row + (uint32_t)half * kBlkBytes, r7, c, pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]);
-      after_half(half);
+    for (int e = 0; e < 16; ++e) {
+      const float a = exp2_fma(__uint_as_float(sv[c][2 * e]), scale_log2, neg_m);
+      const float b = exp2_fma(__uint_as_float(sv[c][2 * e + 1]), scale_log2, neg_m);
+      s0 += a;
+      s1 += b;
+      pw[e] = pack_bf16x2(a, b);
     }
+    tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
+    constexpr int kFirst = NCH > 1 ? 1 : 0;         // hand P over in two halves: PV starts on the first
+    if (!rescale && (c == kFirst || c == NCH - 1)) { // while the second is still in the exp unit
+      tmem_wait_st();
+      tc_fence_before();
+      if (c == kFirst) mbar_arrive(bar_p0);
+      if (c == NCH - 1) mbar_arrive(bar_p1);
+    }
+  }
+  }
+  if (rescale) {                                    // O must carry the new scale before PV(j) accumulates into it
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t ov[32];
+      tmem_ld_32x32b_x32(tO + c * 32, ov);
+      tmem_wait_ld();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) ov[e] = __float_as_uint(__uint_as_float(ov[e]) * alpha);
+      tmem_st_32x32b_x32(tO + c * 32, ov);
+    }
+    tmem_wait_st();
+    tc_fence_before();
+    mbar_arrive(bar_p0);
+    mbar_arrive(bar_p1);
   }
   l_run = l_run * alpha + (s0 + s1);
 }
+
 
 // =====================================================================================================
 // The pipeline is PERSISTENT.
@@ -339,15 +296,11 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 constexpr int kItemRing = 4;
 constexpr int kPlanThreads = 1024;
 constexpr int kPlanBuckets = 1024;
+constexpr int kDecodeCtrlBytes = 64;    // control block of b200_decode at the start of a shared workspace: left untouched
 constexpr int kWorkHeaderInts = 16;     // [0] work counter, [1] number of (sequence, tile) pairs
 // Dynamic shared memory: 2 Q tiles + 4-slot K/V ring + one 32 KiB tile the softmax warps stage output rows in.
-constexpr int kWsOffP = kWsOffRing + kRing * kTileBytes2;       // P_0, P_1: two [128 x 64] bf16 blocks (2 x 16 KiB) per query tile
-constexpr int kWsOffStage = kWsOffP;                            // the epilogue stages output rows in the (then idle) P blocks
-constexpr int kPersistSmem = kWsOffP + 2 * kTileBytes2 + 1024;
-
-// Ring order of one item's 2J tile fills == the order the MMA warp releases them:  K0 K1 V0 K2 V1 ... K(J-1) V(J-2) V(J-1)
-__device__ __forceinline__ int ring_seq_k(int j) { return j == 0 ? 0 : 2 * j - 1; }
-__device__ __forceinline__ int ring_seq_v(int j, int J) { return j + 1 < J ? 2 * j + 2 : 2 * J - 1; }
+constexpr int kWsOffStage = kWsOffRing + kRing * kTileBytes2;   // persistent kernel only
+constexpr int kPersistSmem = kWsOffStage + kTileBytes2 + 1024;
 
 struct ItemDesc {
   int s, kvh, j0, Lq, Lkv, q0, page0, valid;
@@ -425,7 +378,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
                                                                                const __grid_constant__ CUtensorMap tm_v) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing + 6];
+  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing];
   __shared__ __align__(16) ItemDesc s_items[kItemRing];
   __shared__ __align__(16) int s_slots[2][2][2][32];   // cp.async producers: [tile parity][warp][row parity][i]
 
@@ -434,6 +387,17 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   const int G = 1 << log2_g;
   const int tok_per_tile = kTM >> log2_g;
   const int tok_per_cta = 2 * tok_per_tile;
+  // Trimmed last tiles: 32-column chunks of KV tile j that hold columns below the query tile's kv_hi.  Bench-shaped
+  // prompts (100..1024 tokens) own 1..8 KV tiles per item and the last one of each query tile is only
+  // partly valid (causal diagonal of a 32/64-token packed tile, ragged sequence end): QK, softmax and PV
+  // run on 32*nch columns instead of 128 (8-12 % of all chunk steps on the bench prompts).
+  // Compile-time switches, set from a same-box A/B on B200 of a build that had them as run-time flags
+  // (profiles/r1_s38_prefill_flags_ab.txt; bench prompts Hq32 / uniform 16x4096 Hq32, fraction of bf16 peak):
+  //   none 0.303 / 0.633   trim 0.298 / 0.640   staged 0.319 / 0.650   lean_q 0.326 / 0.648   all three 0.291 / 0.670
+  // Trimming costs more than it saves on short prompts (four masked-softmax instances; the kernel is ~7000 SASS
+  // instructions and every extra hot path shows), so it stays off; dead branches are removed by the compiler.
+  constexpr bool trim = false, staged = true, lean_q = true;
+  auto chunks_of = [&](int kv_hi, int j) { return trim ? min(4, (kv_hi - j * kTN + 31) >> 5) : 4; };
 
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
@@ -445,8 +409,6 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   auto bar_o = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 6 + t); };
   auto bar_ifull = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + slot); };
   auto bar_iempty = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + kItemRing + slot); };
-  auto bar_sfree = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + t); };      // S_t is in registers
-  auto bar_pfree = [&](int t, int half) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + 2 + 2 * t + half); };  // PV has read that half of P_t
   constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 TMA warps (lane 0 of each arrives)
 
   if (tid == 0) {
@@ -461,9 +423,6 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_init(bar_p(t, 0), 128);
       mbar_init(bar_p(t, 1), 128);
       mbar_init(bar_o(t), 1);
-      mbar_init(bar_sfree(t), 128);
-      mbar_init(bar_pfree(t, 0), 1);
-      mbar_init(bar_pfree(t, 1), 1);
     }
     for (int i = 0; i < kItemRing; ++i) {
       mbar_init(bar_ifull(i), 1);
@@ -549,7 +508,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
     int qn = 0;
     if (tma_kv) {
       const CUtensorMap* tm = lw ? &tm_v : &tm_k;
-      int gbase = 0;                                   // ring fills of all previous items
+      int fill = lw;                                   // running ring-fill index of this warp's next tile
       for (int it = 0;; ++it) {
         const ItemDesc d = take_item(it);
         if (!d.valid) break;
@@ -577,8 +536,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         }
         ++qn;
         const int col = d.kvh * kTD;
-        for (int tile = 0; tile < g.J; ++tile) {
-          const int fill = gbase + (lw ? ring_seq_v(tile, g.J) : ring_seq_k(tile));
+        for (int tile = 0; tile < g.J; ++tile, fill += 2) {
           const int slot = fill % kRing, use = fill / kRing;
           if (tile + 1 < g.J) ldg_slots(tile + 1, sn);      // in flight behind this tile's issue loop
           mbar_wait(bar_empty(slot), (use & 1) ^ 1);
@@ -591,7 +549,6 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
 #pragma unroll
           for (int i = 0; i < 4; ++i) sl[i] = sn[i];
         }
-        gbase += 2 * g.J;
       }
     } else {
       const int lt = tid - 9 * 32;                    // 0..63
@@ -625,7 +582,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           mbar_wait(bar, parity);
         }
       };
-      int gbase = 0;                                   // ring fills of all previous items
+      int kc = 0, vc = 0;                              // K / V tiles filled so far (whole kernel)
       for (int it = 0;; ++it) {
         wait_or_flush(bar_ifull(it % kItemRing), (it / kItemRing) & 1);
         const ItemDesc d = take_item(it);
@@ -665,8 +622,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         }
         const char* kbase = reinterpret_cast<const char*>(p.k_cache + (int64_t)d.kvh * kTD + gc * 8);
         const char* vbase = reinterpret_cast<const char*>(p.v_cache + (int64_t)d.kvh * kTD + gc * 8);
-        auto fill_tile = [&](const char* base, int tile, int fill) {
-          const int slot = fill % kRing, use = fill / kRing;
+        auto fill_tile = [&](const char* base, int tile, int slot, int use) {
           __syncwarp();
           int sl[32];
           const int4* src = reinterpret_cast<const int4*>(&s_slots[tile & 1][lw][hrow][0]);
@@ -691,45 +647,38 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           }
           rotate(bar_full(slot));
         };
-        fill_tile(kbase, 0, gbase);
+        fill_tile(kbase, 0, 2 * (kc & 1), kc >> 1);
+        ++kc;
         for (int j = 0; j < g.J; ++j) {
           if (j + 2 < g.J) ldg_pages(j + 2);               // consumed after V(j) has been issued
-          if (j + 1 < g.J) fill_tile(kbase, j + 1, gbase + ring_seq_k(j + 1));
-          fill_tile(vbase, j, gbase + ring_seq_v(j, g.J));
+          if (j + 1 < g.J) {
+            fill_tile(kbase, j + 1, 2 * (kc & 1), kc >> 1);
+            ++kc;
+          }
+          fill_tile(vbase, j, 2 * (vc & 1) + 1, vc >> 1);
+          ++vc;
           if (j + 2 < g.J) {
             __syncwarp();                                  // V(j) has read tile j's slot ids: its parity is free
             put_slots(j + 2);
           }
         }
-        gbase += 2 * g.J;
       }
       flush();
     }
   } else if (warp == 8) {
     // =================================== MMA issuer =======================================================
-    // Issue order per KV tile j:   QK_0(j+1) QK_1(j+1)   PV_0(j) PV_1(j)
-    // QK(j+1) needs only K(j+1) and S_t to be free, which the softmax group signals right after it has pulled
-    // S_t(j) into registers, so the tensor pipe computes the NEXT scores under the CURRENT tile's exponentials and the
-    // softmax groups never wait for a QK in steady state.  PV_t(j) follows P_t(j) half by half (two 64-token halves
-    // through one shared-memory block per query tile; A and B both from shared memory).
     asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
-    constexpr uint32_t idesc_qk = make_idesc_bf16_f32(kTM, kTN, 0, 0);
+    constexpr uint32_t idesc_qk0 = make_idesc_bf16_f32(kTM, 0, 0, 0);             // N field filled per tile
     constexpr uint32_t idesc_pv = make_idesc_bf16_f32(kTM, kTD, 0, 1);
     const uint64_t qdesc0 = make_smem_desc(smem + kWsOffQ, 16, 1024);
     const uint64_t kdesc0 = make_smem_desc(smem + kWsOffRing, 16, 1024);          // K tiles: K-major
     const uint64_t vdesc0 = make_smem_desc(smem + kWsOffRing, kBlkBytes, 1024);   // V tiles: MN-major
-    const uint64_t pdesc0 = make_smem_desc(smem + kWsOffP, 16, 1024);             // P blocks: K-major, 64 tokens wide
-    int qkc[2] = {0, 0};          // QK_t issued so far (whole kernel) == S_t tiles handed to softmax group t
-    int pc[2] = {0, 0};           // P_t tiles consumed so far
-    // f = running ring-fill index of the K tile
-    auto issue_qk = [&](int t, int f) {
-      if (qkc[t] > 0) {                                  // softmax group t has read the previous S_t out of TMEM
-        mbar_wait(bar_sfree(t), (qkc[t] - 1) & 1);
-        tc_fence_after();
-      }
-      ++qkc[t];
+    // f = running ring-fill index of the K tile; nch = 32-column chunks of S to produce (N = 32 * nch: the
+    // first N token rows of the K-major tile)
+    auto issue_qk = [&](int t, int f, int nch) {
       const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
       const uint64_t kd = kdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
+      const uint32_t idesc_qk = idesc_qk0 | ((uint32_t)(nch << 2) << 17);
 #pragma unroll
       for (int ks = 0; ks < kTD / 16; ++ks) {
         const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
@@ -737,17 +686,17 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       }
       umma_commit_elect(bar_s(t));
     };
-    // f = running ring-fill index of the V tile; half = 64-token half of the tile (4 K steps of 16 tokens)
-    auto issue_pv_half = [&](int t, int f, int half, bool acc) {
-      const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4)) + (uint64_t)(half * 4 * (2048 >> 4));
-      const uint64_t pd = pdesc0 + (uint64_t)((2 * t + half) * (kBlkBytes >> 4));
+    // f = running ring-fill index of the V tile; nks = 16-token K steps holding valid P columns (2 per chunk)
+    auto issue_pv = [&](int t, int f, int half, bool acc, int nks) {
+      const uint64_t vd = vdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4));
 #pragma unroll
-      for (int ks = 0; ks < 4; ++ks)
-        umma_ss_elect(tmem + 2 * kTN + t * kTD, pd + (uint64_t)(ks * (32 >> 4)), vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
-                      (acc || ks > 0));
-      umma_commit_elect(bar_pfree(t, half));
+      for (int ks = half * 4; ks < half * 4 + 4; ++ks)
+        if (ks < nks)
+          umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
+                        (acc || ks > 0));
     };
     int fillc = 0, qn = 0;
+    int pc[2] = {0, 0};
     for (int it = 0;; ++it) {
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
@@ -757,37 +706,41 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_wait(bar_q, qn & 1);
       mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
       tc_fence_after();
-      if (g.nt0 > 0) issue_qk(0, base);
-      if (g.nt1 > 0) issue_qk(1, base);
+      if (g.nt0 > 0) issue_qk(0, base, chunks_of(g.kvhi0, 0));
+      if (g.nt1 > 0) issue_qk(1, base, chunks_of(g.kvhi1, 0));
       umma_commit_elect(bar_empty(base % kRing));                        // K(0) free once both QK(0) are done
       if (g.J == 1) umma_commit_elect(bar_qfree);                        // last QK of the item: Q may be refilled
       for (int j = 0; j < g.J; ++j) {
-        const int fv = base + ring_seq_v(j, g.J), fk = base + ring_seq_k(j + 1);
-        if (j + 1 < g.J) {                                               // scores of the NEXT tile, under this tile's softmax
-          mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);             // K(j+1)
-          tc_fence_after();
-          if (j + 1 < g.nt0) issue_qk(0, fk);
-          if (j + 1 < g.nt1) issue_qk(1, fk);
-          umma_commit_elect(bar_empty(fk % kRing));
-          if (j + 2 == g.J) umma_commit_elect(bar_qfree);
-        }
+        const int fv = base + 2 * j + 1, fk = base + 2 * j + 2;
         mbar_wait(bar_full(fv % kRing), (fv / kRing) & 1);               // V(j)
-        tc_fence_after();
+        bool k_ready = false;
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
           const int ntt = t ? g.nt1 : g.nt0;
+          const int kvhit = t ? g.kvhi1 : g.kvhi0;
           if (j < ntt) {
-            mbar_wait(bar_p(t, 0), pc[t] & 1);                           // tokens 0..63 of P_t(j) are in shared memory
+            const int nks = 2 * chunks_of(kvhit, j);
+            mbar_wait(bar_p(t, 0), pc[t] & 1);                           // first 64 columns of P_t(j) are in TMEM
             tc_fence_after();
-            issue_pv_half(t, fv, 0, j > 0);
-            mbar_wait(bar_p(t, 1), pc[t] & 1);                           // tokens 64..127 (same block, rewritten)
+            issue_pv(t, fv, 0, j > 0, nks);
+            mbar_wait(bar_p(t, 1), pc[t] & 1);                           // the rest
             tc_fence_after();
-            issue_pv_half(t, fv, 1, true);
+            issue_pv(t, fv, 1, true, nks);
             ++pc[t];
             if (j == ntt - 1) umma_commit_elect(bar_o(t));
           }
+          if (j + 1 < ntt) {
+            if (!k_ready) {
+              mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);         // K(j+1)
+              tc_fence_after();
+              k_ready = true;
+            }
+            issue_qk(t, fk, chunks_of(kvhit, j + 1));
+          }
         }
         umma_commit_elect(bar_empty(fv % kRing));
+        if (j + 1 < g.J) umma_commit_elect(bar_empty(fk % kRing));
+        if (j + 2 == g.J) umma_commit_elect(bar_qfree);
       }
       fillc += 2 * g.J;
       ++qn;
@@ -800,8 +753,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem + lane_base + t * kTN;
     const uint32_t tO = tmem + lane_base + 2 * kTN + t * kTD;
-    const uint32_t p_row = smem + kWsOffP + (uint32_t)t * kTileBytes2 + (uint32_t)r * 128u;   // my row of P_t's first block
-    int sc = 0, oc = 0;                               // sc = S / P tiles of this group so far (whole kernel)
+    int sc = 0, oc = 0;
     for (int it = 0;; ++it) {
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
@@ -820,11 +772,14 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
         if (need_mask) {
           const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
-          softmax_tile<true>(tS, tO, nvalid, p.scale_log2, m_used, l_run, p_row, r & 7, bar_sfree(t), bar_p(t, 0), bar_p(t, 1),
-                             bar_pfree(t, 0), sc);
+          switch (chunks_of(kv_hi, j)) {                              // tile-uniform
+            case 1: softmax_tile<true, 1>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+            case 2: softmax_tile<true, 2>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+            case 3: softmax_tile<true, 3>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+            default: softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
+          }
         } else {
-          softmax_tile<false>(tS, tO, kTN, p.scale_log2, m_used, l_run, p_row, r & 7, bar_sfree(t), bar_p(t, 0), bar_p(t, 1),
-                              bar_pfree(t, 0), sc);
+          softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
         }
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
@@ -839,19 +794,45 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       // (8 lanes per row); straight from the TMEM layout (thread = row) a warp store touches 32 lines with 16 bytes
       // each and the 8 softmax warps spent ~4000 LSU wavefront-cycles per item in the epilogue (14 % of their
       // time on bench-shaped prompts).  Staging area, 4 KiB per warp (32 rows x 64 columns bf16, 16-byte pieces
-      // XOR-swizzled by row): this warp's own 32 rows of the P_t block, idle once bar_o says every PV_t has read it.
-      const uint32_t stage = smem + kWsOffStage + (uint32_t)t * kTileBytes2 + (uint32_t)(warp & 3) * 4096u;
+      // XOR-swizzled by row): the 7th operand tile, touched by nobody else.
+      const uint32_t stage = smem + kWsOffStage + (uint32_t)warp * 4096u;
       const int rows_ok = tokst << log2_g;
       const int rsub = lane >> 3, piece = lane & 7;
-      if (!has && r < rows_ok) {
-        // rows without any visible KV (Lkv == 0, or causal with Lkv < Lq) are zeros
-        uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + my_tok) * p.out_row_stride +
-                                              (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+      if (!has || !staged) {
+        // thread = row, straight from the TMEM layout.  Rows without any visible KV (Lkv == 0, or causal with
+        // Lkv < Lq) are zeros; with data this is the unstaged form kept for A/B measurements.
+        if (r < rows_ok) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + my_tok) * p.out_row_stride +
+                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+          if (!has) {
 #pragma unroll
-        for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
+            for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+        if (has) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + (r < rows_ok ? my_tok : d.j0)) * p.out_row_stride +
+                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t ov[32];
+            tmem_ld_32x32b_x32(tO + c * 32, ov);
+            tmem_wait_ld();
+            if (r < rows_ok) {
+#pragma unroll
+              for (int j8 = 0; j8 < 4; ++j8) {
+                uint4 w;
+                w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+                w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+                w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+                w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+                dst[c * 4 + j8] = w;
+              }
+            }
+          }
+        }
       }
 #pragma unroll
-      for (int half = 0; half < 2 && has; ++half) {
+      for (int half = 0; half < 2 && has && staged; ++half) {
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
           uint32_t ov[32];
@@ -897,7 +878,7 @@ size_t prefill_sm100_workspace_bytes(int B, int total_q, int group) {
   while ((1 << log2_g) < group) ++log2_g;
   const int tok_per_cta = 2 * (kTM >> log2_g);
   const size_t max_pairs = (size_t)total_q / tok_per_cta + (size_t)B;
-  return kWorkHeaderInts * sizeof(int) + max_pairs * sizeof(int2);
+  return kDecodeCtrlBytes + kWorkHeaderInts * sizeof(int) + max_pairs * sizeof(int2);
 }
 
 int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, size_t workspace_bytes, cudaStream_t st) {
@@ -911,9 +892,9 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   static std::atomic<bool> attr_done[64];
   if (cudaError_t e = ensure_dyn_smem(prefill_sm100_persist_kernel, kPersistSmem, attr_done); e != cudaSuccess)
     return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-  int* work = reinterpret_cast<int*>(workspace);
+  int* work = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + kDecodeCtrlBytes);   // b200_decode owns the first 64 bytes
   int2* items = reinterpret_cast<int2*>(work + kWorkHeaderInts);
-  const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
+  const int max_pairs = (int)((workspace_bytes - kDecodeCtrlBytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
   prefill_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, 2 * tok_per_tile, work, items, max_pairs);
   if (int rc = check_launch("b200_prefill(plan)")) return rc;
   // Tensor maps (host-encoded per call: q and the layer's pool pointers change between calls; the maps travel as

@@ -317,6 +317,49 @@ def test_decode_properties_long_context(pkg):
     assert (o1[b, h] - p @ V).abs().max() <= 2e-2
 
 
+@pytest.mark.parametrize("ps", [16, 1])
+def test_decode_dynamic_split_one_kv_head(pkg, ps):
+    """Ranks with ONE KV head and ~1.4 M tokens of context take the guided dynamic split (chunks claimed from the
+    counter in the workspace's control block).  Ragged lengths, every output row against a direct fp32 computation on
+    the device; the same workspace serves a prefill call in between and three decode calls (the counter is
+    re-armed by every call); repeated calls agree within tolerance (the order of claims is not deterministic, the
+    partials are merged in fp32)."""
+    torch.manual_seed(1)
+    rng = np.random.default_rng(3)
+    B, Hq, Hkv, D = 48, 4, 1, 128
+    lens = rng.integers(20000, 40000, B)
+    lens[5], lens[17] = 3, 70001
+    pages = -(-lens // ps)
+    n_pages = int(pages.sum())
+    k_cache = torch.randn((n_pages * ps, Hkv, D), device="cuda", dtype=torch.bfloat16)
+    v_cache = torch.randn_like(k_cache)
+    q = torch.randn((B, Hq, D), device="cuda", dtype=torch.bfloat16)
+    perm = torch.from_numpy(rng.permutation(n_pages).astype(np.int32)).cuda()
+    indptr_np = np.concatenate([[0], np.cumsum(pages)]).astype(np.int32)
+    indptr = torch.from_numpy(indptr_np).cuda()
+    last = torch.from_numpy((lens - (pages - 1) * ps).astype(np.int32)).cuda()
+    ws = _ws(pkg, B, Hq, Hkv, D, total_q=4096)
+    sm = D ** -0.5
+    outs = []
+    for rep in range(3):
+        outs.append(pkg.ops.decode(q, k_cache, v_cache, indptr, perm, last, ws, ps, sm).float())
+        if rep == 0:    # a prefill through the SAME workspace must leave the decode control block alone
+            case = make_paged_case([300, 77], Hq, Hkv, q_lens=[300, 77], seed=4)
+            d = dev(case)
+            pkg.ops.prefill(d["q"], d["k_cache"], d["v_cache"], d["qo_indptr"], d["kv_indptr"], d["kv_indices"],
+                            d["last_page_len"], ws, 1, sm, True)
+    torch.cuda.synchronize()
+    assert (outs[0] - outs[1]).abs().max() <= 1e-2 and (outs[0] - outs[2]).abs().max() <= 1e-2
+    worst = 0.0
+    for b in range(B):
+        pg = perm[indptr_np[b]:indptr_np[b + 1]].long()
+        slots = (pg[:, None] * ps + torch.arange(ps, device="cuda")[None]).view(-1)[:int(lens[b])]
+        K, V = k_cache[slots, 0].float(), v_cache[slots, 0].float()
+        p = torch.softmax((q[b].float() @ K.T) * sm, -1)
+        worst = max(worst, float((outs[0][b] - p @ V).abs().max()))
+    assert worst <= 2e-2, worst
+
+
 @pytest.mark.gpu
 def test_prefill_properties_full_bench_step(pkg):
     """One prefill step of the WHOLE bench workload (BASELINE.json configs[2]: 256 prompts, 142 827 tokens,
