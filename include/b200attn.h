@@ -116,18 +116,10 @@ int b200_build_meta(const int32_t* slot_table, int64_t table_row_stride, const i
  *     kv_indptr   : int32 [B+1]; kv_indices: page ids; last_page_len: int32 [B]
  *     page_size   : power of two; token t of a sequence lives in slot
  *                   kv_indices[indptr + t / ps] * ps + t % ps
- *     workspace   : >= b200_decode_workspace_bytes(B, Hq, Hkv, D) bytes, 16-byte aligned.  Its first 64 bytes
- *                   are a control block that lives ACROSS calls (the chunk counter of the dynamic split-KV
- *                   schedule, reset by every call for the next one): run b200_decode_workspace_init ONCE on
- *                   a freshly allocated buffer before its first b200_decode, and do not let other kernels
- *                   write those 64 bytes (b200_prefill leaves them alone, so one buffer can serve both).
- *                   A call on a buffer that was never initialised traps on the device instead of computing
- *                   a wrong result (only ranks with one KV head use the counter).
+ *     workspace   : >= b200_decode_workspace_bytes(B, Hq, Hkv, D) bytes, 16-byte aligned
  *     Only D == 128 and dtype bf16 are built in round 1.
  * ---------------------------------------------------------------------------------------- */
 size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D);
-
-int b200_decode_workspace_init(void* workspace, size_t workspace_bytes, b200_stream_t stream);
 
 int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
                 int64_t kv_slot_stride, const int32_t* kv_indptr, const int32_t* kv_indices,

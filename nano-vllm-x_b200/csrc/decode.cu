@@ -19,13 +19,6 @@
 //    q rows fetched when the producer crosses into it) runs across segment boundaries, so short
 //    sequences (the engine's decode batches: B 256, L <= 2048) do not pay a pipeline refill per
 //    sequence.  No __syncthreads after the prologue, no combine inside the CTA.
-//  * Hkv = 1 per rank (TP8 shapes: every warp is its own stream) and long contexts: the streams do not get equal
-//    shares of HBM bandwidth (ncu: SM active cycles min / avg / max = 76 / 84 / 98 % of the kernel at config 5,
-//    profiles/r2_s7_decode_tp8_*), so a static split leaves 16 % of the machine idle.  There the tile list is cut
-//    into 6*streams CHUNKS of three sizes (8u, 4u, u tiles; u = total / (16*streams)) that the warps claim from an
-//    atomic counter, largest first (guided self-scheduling); the claim for the next chunk is made by the producer
-//    cursor, three tiles before the math reaches the end of the current one, so the pipeline still never drains.
-//    Partial slot = chunk id + s (chunks are ordered like streams).
 //  * Prologue: ONE block scan of the batch's tile counts (inclusive prefix kept in shared
 //    memory), then every warp binary-searches the sequence its stream starts in.
 //  * q.K^T and p.V use mma.sync m16n8k16 (bf16 in, fp32 accumulate) fed by ldmatrix; decode is
@@ -50,10 +43,6 @@ constexpr int kWarpSmem = kStages * kStageBytes;       // 24 KiB
 constexpr int kDecodeSmem = kWarps * kWarpSmem;        // 192 KiB
 constexpr int kMinTilesPerStream = 2;  // do not split finer than 32 tokens per stream
 constexpr int kMaxSmemSeqs = 4096;     // batches up to this size keep their tile prefix in shared memory
-constexpr int kMinDynUnit = 4;         // dynamic chunks are >= 4 tiles (> the producer's 3-tile lookahead)
-constexpr int kDynChunksPerStream = 6; // 1 of 8u + 1 of 4u + 4 of u tiles per stream
-constexpr int kCtrlBytes = 64;         // control block at the start of the workspace (survives between calls)
-constexpr unsigned long long kCtrlMagic = 0xB200DEC0ull << 32;   // high word of a control word that was initialised
 
 struct DecodeParams {
   const __nv_bfloat16* q;
@@ -67,7 +56,6 @@ struct DecodeParams {
   float* part_lse;    // [G*subs+B][Hq]
   int32_t* seg_first; // [B]
   int32_t* seg_last;  // [B]
-  unsigned long long* counter;   // control word {magic : 32, chunks claimed : 32} or nullptr: static split only
   int64_t q_row_stride, out_row_stride, kv_slot_stride;
   int B, Hq, Hkv, group, log2_ps;
   int heads_per_cta;  // KV heads handled by one CTA (<= 8)
@@ -109,83 +97,43 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   const int k_stream = sub * G + blockIdx.x;       // consecutive streams sit on different SMs
   int per = (total + n_streams - 1) / n_streams;
   if (per < kMinTilesPerStream) per = kMinTilesPerStream;
-  const int unit = (total + 16 * n_streams - 1) / (16 * n_streams);
-  const bool dyn = p.counter != nullptr && in_smem && unit >= kMinDynUnit;   // same decision in every CTA
+  const int t_begin = k_stream * per;
+  if (t_begin >= total) return;
+  const int t_end = min(t_begin + per, total);
 
-  // chunk `cid` of the tile list: the static split has one chunk per stream (cid = stream); the dynamic split hands
-  // out n_streams chunks of 8u tiles, n_streams of 4u, then chunks of u, in list order
-  bool claimed_static = false;
-  auto claim = [&](int& cb, int& ce, int& cid) -> bool {
-    if (!dyn) {
-      if (claimed_static) return false;
-      claimed_static = true;
-      cid = k_stream;
-      cb = k_stream * per;
-      ce = min(cb + per, total);
-      return cb < total;
+  // ---- the sequence this stream starts in: smallest s with incl(s) > t_begin ----------------------
+  int s0, pre0;
+  if (in_smem) {
+    int lo = 0, hi = p.B - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (s_incl[mid] > t_begin) hi = mid; else lo = mid + 1;
     }
-    int c = 0;
-    if (lane == 0) {
-      const unsigned long long v = atomicAdd(p.counter, 1ull);
-      if ((v >> 32) != (kCtrlMagic >> 32)) __trap();   // workspace never went through b200_decode_workspace_init
-      c = (int)(unsigned)v;
-    }
-    c = __shfl_sync(0xffffffffu, c, 0);
-    if (c < n_streams) {
-      cb = c * 8 * unit;
-      ce = cb + 8 * unit;
-    } else if (c < 2 * n_streams) {
-      cb = (8 * n_streams + 4 * (c - n_streams)) * unit;
-      ce = cb + 4 * unit;
-    } else {
-      if (c >= kDynChunksPerStream * n_streams) return false;
-      cb = (12 * n_streams + (c - 2 * n_streams)) * unit;
-      ce = cb + unit;
-    }
-    if (cb >= total) return false;
-    ce = min(ce, total);
-    cid = c;
-    return true;
-  };
-  // the sequence that holds flat tile t: smallest s with incl(s) > t
-  auto locate = [&](int t, int& s_out, int& pre_out) {
-    if (in_smem) {
-      int lo = 0, hi = p.B - 1;
-      while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (s_incl[mid] > t) hi = mid; else lo = mid + 1;
-      }
-      s_out = lo;
-      pre_out = lo > 0 ? s_incl[lo - 1] : 0;
-      return;
-    }
+    s0 = lo;
+    pre0 = lo > 0 ? s_incl[lo - 1] : 0;
+  } else {
     int carry = 0;
-    s_out = pre_out = 0;
+    s0 = pre0 = 0;
     for (int base = 0; base < p.B; base += 32) {
       const int i = base + lane;
-      const int tl = i < p.B ? tiles_of(p, i) : 0;
-      int x = tl;
+      const int t = i < p.B ? tiles_of(p, i) : 0;
+      int x = t;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const int y = __shfl_up_sync(0xffffffffu, x, o);
         if (lane >= o) x += y;
       }
       x += carry;
-      const unsigned m = __ballot_sync(0xffffffffu, x > t);
+      const unsigned m = __ballot_sync(0xffffffffu, x > t_begin);
       if (m) {
         const int l = __ffs(m) - 1;
-        s_out = base + l;
-        pre_out = __shfl_sync(0xffffffffu, x, l) - __shfl_sync(0xffffffffu, tl, l);
-        return;
+        s0 = base + l;
+        pre0 = __shfl_sync(0xffffffffu, x, l) - __shfl_sync(0xffffffffu, t, l);
+        break;
       }
       carry = __shfl_sync(0xffffffffu, x, 31);
     }
-  };
-
-  int cb, ce, ccid;                                // the chunk the math is in
-  if (!claim(cb, ce, ccid)) return;
-  int s0, pre0;
-  locate(cb, s0, pre0);
+  }
 
   const int kv_head = head_group * p.heads_per_cta + hh;
   const int row = lane >> 2;                        // mma row = query head inside the group
@@ -222,10 +170,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
     }
   };
 
-  // ---- producer cursor: the chunk / sequence that holds the tile whose slot ids are fetched next --------
-  int pt = cb, pe = ce;                            // next flat tile of the producer, end of its chunk
-  bool pdone = false;
-  int nb = 0, ne = 0, ncid = 0, nseq = 0, npre = 0;   // the chunk the producer has moved on to (the math follows later)
+  // ---- producer cursor: the sequence that holds the tile whose slot ids are fetched next -------------
   int ps = s0, ppre = pre0;
   int pL = seq_kv_len(p.kv_indptr, p.last_page_len, ps, p.log2_ps);
   int pnt = (pL + kTile - 1) / kTile;
@@ -233,46 +178,23 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   uint32_t qn[kD / 16][2];          // q rows of the sequence the producer is in
   int qn_s = ps;
   load_q(ps, qn);
-  // slot id of row (lane & 15) of the producer's next tile, fetched one tile ahead of its copies; false: no tile left
-  auto fetch_next = [&](int& slot) -> bool {
-    if (pdone) return false;
-    bool moved = false;
-    if (pt == pe) {
-      int b2, e2, c2;
-      if (!claim(b2, e2, c2)) {
-        pdone = true;
-        return false;
-      }
-      pt = b2;
-      pe = e2;
-      locate(b2, ps, ppre);
-      nb = b2; ne = e2; ncid = c2; nseq = ps; npre = ppre;
-      pL = seq_kv_len(p.kv_indptr, p.last_page_len, ps, p.log2_ps);
-      pnt = (pL + kTile - 1) / kTile;
-      moved = true;
-    }
-    if (pt >= ppre + pnt) {
+  // slot id of row (lane & 15) of flat tile ti, fetched one tile ahead of its copies
+  auto fetch_slot = [&](int ti) -> int {
+    if (ti >= ppre + pnt) {
       do {
         ppre += pnt;
         ++ps;
         pL = seq_kv_len(p.kv_indptr, p.last_page_len, ps, p.log2_ps);
         pnt = (pL + kTile - 1) / kTile;
-      } while (pt >= ppre + pnt);
-      moved = true;
-    }
-    if (moved) {
+      } while (ti >= ppre + pnt);
       ppage0 = p.kv_indptr[ps];
       load_q(ps, qn);
       qn_s = ps;
     }
-    const int tok = (pt - ppre) * kTile + (lane & 15);
-    ++pt;
-    slot = -1;
-    if (tok < pL) {
-      const int page = __ldg(p.kv_indices + ppage0 + (tok >> p.log2_ps));
-      slot = (page << p.log2_ps) + (tok & ps_mask);
-    }
-    return true;
+    const int tok = (ti - ppre) * kTile + (lane & 15);
+    if (tok >= pL) return -1;
+    const int page = __ldg(p.kv_indices + ppage0 + (tok >> p.log2_ps));
+    return (page << p.log2_ps) + (tok & ps_mask);
   };
   auto issue = [&](int it, int my_slot) {
     const uint32_t st = warp_smem + (it % kStages) * kStageBytes;
@@ -288,22 +210,19 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
     }
   };
 
-  int next_slot = -1;
-  bool next_ok = fetch_next(next_slot);
-  int issued = 0;                                  // tiles handed to the copy pipeline so far
+  const int n_my = t_end - t_begin;
+  int next_slot = fetch_slot(t_begin);
 #pragma unroll
   for (int it = 0; it < kStages - 1; ++it) {
-    if (next_ok) {
+    if (it < n_my) {
       const int cur = next_slot;
-      next_ok = fetch_next(next_slot);
+      next_slot = (it + 1 < n_my) ? fetch_slot(t_begin + it + 1) : -1;
       issue(it, cur);
-      ++issued;
     }
     cp_async_commit();
   }
 
   // ---- consumer cursor ---------------------------------------------------------------------------
-  int ct = cb;                                     // flat tile of the math
   int cs = s0, cpre = pre0;
   int cL = seq_kv_len(p.kv_indptr, p.last_page_len, cs, p.log2_ps);
   int cnt = (cL + kTile - 1) / kTile;
@@ -312,22 +231,17 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   float m_run = -INFINITY, l_run = 0.f;
   bool seg_start = true;
 
-  for (int it = 0; it < issued; ++it) {
-    if (next_ok) {
-      const int cur = next_slot;
-      next_ok = fetch_next(next_slot);
-      issue(it + kStages - 1, cur);
-      ++issued;
+  for (int it = 0; it < n_my; ++it) {
+    {
+      const int nx = it + kStages - 1;
+      if (nx < n_my) {
+        const int cur = next_slot;
+        next_slot = (nx + 1 < n_my) ? fetch_slot(t_begin + nx + 1) : -1;
+        issue(nx, cur);
+      }
+      cp_async_commit();
     }
-    cp_async_commit();
-    if (ct == ce) {                                // the math moves on to the chunk the producer claimed earlier
-      cb = nb; ce = ne; ccid = ncid; ct = nb;
-      cs = nseq; cpre = npre;
-      cL = seq_kv_len(p.kv_indptr, p.last_page_len, cs, p.log2_ps);
-      cnt = (cL + kTile - 1) / kTile;
-      seg_start = true;
-    }
-    const int ti = ct++;
+    const int ti = t_begin + it;
     if (ti >= cpre + cnt) {
       do {
         cpre += cnt;
@@ -411,10 +325,10 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
     __syncwarp();
 
     // ---- segment epilogue: last tile of this sequence inside this stream -----------------------------
-    const int seg_e = min(ce, cpre + cnt) - cpre;
+    const int seg_e = min(t_end, cpre + cnt) - cpre;
     if (tile + 1 == seg_e) {
-      const int seg_b = max(cb, cpre) - cpre;
-      const int slot_id = ccid + cs;         // unique per (chunk, sequence) segment, see header
+      const int seg_b = max(t_begin, cpre) - cpre;
+      const int slot_id = k_stream + cs;     // unique per (stream, sequence) segment, see header
       const bool whole = (seg_b == 0) && (seg_e == cnt);
       if (lane == 0 && hh == 0 && head_group == 0) {
         if (seg_b == 0) p.seg_first[cs] = slot_id;
@@ -443,74 +357,50 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   cp_async_wait<0>();
 }
 
-// Merge pass: one CTA per (sequence, query head), 8 warps.  The log-sum-exps of the partial list are read lane-parallel
-// (one round trip for up to 256 partials), their maximum and the weights go through shared memory, then the warps split
-// the list, a lane owns 4 output dims (float4 loads: one coalesced 512-byte row per partial per warp) with 8 loads in
-// flight per lane, and combine through shared memory.  With the dynamic split a long sequence owns ~100 partials:
-// the 4-warp two-pass version spent ~14 dependent round trips on them.
-constexpr int kMergeThreads = 256;
-constexpr int kMergeWarps = kMergeThreads / 32;
-constexpr int kMergeMaxW = 1024;      // weights kept in shared memory; longer lists recompute them from the lse
-__global__ void __launch_bounds__(kMergeThreads) decode_merge_kernel(const DecodeParams p) {
-  const int s = blockIdx.x, hq = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// Merge pass: one CTA per (sequence, query head); 4 warps split the partial list, a lane owns 4 output
+// dims (float4 loads: one coalesced 512-byte row per partial per warp), warps combine through smem.
+__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
+  const int s = blockIdx.x, hq = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD;
-  __shared__ float s_red[kMergeWarps];
-  __shared__ float s_w[kMergeMaxW];
-  __shared__ float4 s_acc[kMergeWarps][32];
   griddep_wait();                     // launched with PDL: partials / segment maps come from decode_kernel
-  // the chunk counter goes back to zero for the next launch (every claim of this launch has been made)
-  if (p.counter != nullptr && s == 0 && hq == 0 && tid == 0) *p.counter = kCtrlMagic;
   const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
   if (L == 0) {
-    if (tid < kD) dst[tid] = __float2bfloat16(0.f);
+    dst[threadIdx.x] = __float2bfloat16(0.f);
     return;
   }
   const int first = p.seg_first[s], last = p.seg_last[s];
   if (first == last) return;  // one segment: written directly by the streaming kernel
   const int n = last - first + 1;
   const float* lse = p.part_lse + (int64_t)first * p.Hq + hq;
-  float mx = -INFINITY;
-  for (int i = tid; i < n; i += kMergeThreads) mx = fmaxf(mx, lse[(int64_t)i * p.Hq]);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  if (lane == 0) s_red[warp] = mx;
-  __syncthreads();
-  mx = s_red[0];
-#pragma unroll
-  for (int w = 1; w < kMergeWarps; ++w) mx = fmaxf(mx, s_red[w]);
-  for (int i = tid; i < min(n, kMergeMaxW); i += kMergeThreads) {
-    const float l = lse[(int64_t)i * p.Hq];           // L1 hit: read a moment ago
-    s_w[i] = l == -INFINITY ? 0.f : fast_exp2(l - mx);
-  }
-  __syncthreads();
   const float4* po = reinterpret_cast<const float4*>(p.part_o + ((int64_t)first * p.Hq + hq) * kD) + lane;
   const int64_t po_stride = (int64_t)p.Hq * kD / 4;
+  __shared__ float s_m[4], s_w[4];
+  __shared__ float4 s_acc[4][32];
+  float mx = -INFINITY;
+  for (int i = warp; i < n; i += 4) mx = fmaxf(mx, lse[(int64_t)i * p.Hq]);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   float wsum = 0.f;
-#pragma unroll 8
-  for (int i = warp; i < n; i += kMergeWarps) {
-    float w;
-    if (i < kMergeMaxW) {
-      w = s_w[i];
-    } else {
-      const float l = lse[(int64_t)i * p.Hq];
-      w = l == -INFINITY ? 0.f : fast_exp2(l - mx);
-    }
+#pragma unroll 4
+  for (int i = warp; i < n; i += 4) {
+    const float l = lse[(int64_t)i * p.Hq];
+    const float w = l == -INFINITY ? 0.f : fast_exp2(l - mx);
     const float4 v = po[(int64_t)i * po_stride];
     wsum += w;
     acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z; acc.w += w * v.w;
   }
-  if (lane == 0) s_red[warp] = wsum;   // (every thread has read the maxima: they were consumed before the last barrier)
+  if (lane == 0) { s_m[warp] = mx; s_w[warp] = wsum; }
   s_acc[warp][lane] = acc;
   __syncthreads();
   if (warp == 0) {
+    const float M = fmaxf(fmaxf(s_m[0], s_m[1]), fmaxf(s_m[2], s_m[3]));
     float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
     float W = 0.f;
 #pragma unroll
-    for (int w = 0; w < kMergeWarps; ++w) {
+    for (int w = 0; w < 4; ++w) {
+      const float f = s_m[w] == -INFINITY ? 0.f : fast_exp2(s_m[w] - M);
       const float4 a = s_acc[w][lane];
-      W += s_red[w];
-      r.x += a.x; r.y += a.y; r.z += a.z; r.w += a.w;
+      W += f * s_w[w];
+      r.x += f * a.x; r.y += f * a.y; r.z += f * a.z; r.w += f * a.w;
     }
     const float inv = W > 0.f ? 1.f / W : 0.f;
     uint2 o2;
@@ -518,10 +408,6 @@ __global__ void __launch_bounds__(kMergeThreads) decode_merge_kernel(const Decod
     o2.y = pack_bf16x2(r.z * inv, r.w * inv);
     *reinterpret_cast<uint2*>(dst + lane * 4) = o2;
   }
-}
-
-__global__ void decode_ws_init_kernel(unsigned long long* ctrl) {
-  if (threadIdx.x == 0) ctrl[0] = kCtrlMagic;
 }
 
 static int ilog2_exact_d(int x) {
@@ -545,15 +431,6 @@ static bool decode_cfg(int Hkv, DecodeCfg* c) {
   return true;
 }
 
-// Dynamic chunk claiming (see the header comment) is built for ranks with ONE KV head, where every warp is its own
-// stream; with more heads the warps of a stream would have to agree on every claim.
-static bool decode_dynamic(const DecodeCfg& c) { return c.heads_per_cta == 1 && c.head_groups == 1; }
-// partial (o, lse) slots: one per (chunk, sequence) intersection, slot = chunk id + sequence index
-static size_t decode_parts(int G, const DecodeCfg& c, int B) {
-  const size_t streams = (size_t)G * c.subs;
-  return (decode_dynamic(c) ? (size_t)kDynChunksPerStream * streams : streams) + (size_t)B;
-}
-
 }  // namespace b200
 
 extern "C" size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv, int32_t D) {
@@ -561,20 +438,11 @@ extern "C" size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv
   DecodeCfg c;
   if (B <= 0 || Hq <= 0 || D <= 0 || !decode_cfg(Hkv, &c)) return 0;
   const int G = cached_num_sms();
-  const size_t parts = decode_parts(G, c, B);
+  const size_t parts = (size_t)G * c.subs + (size_t)B;
   size_t bytes = parts * Hq * D * sizeof(float);       // part_o
   bytes += parts * Hq * sizeof(float);                 // part_lse
   bytes += 2 * (size_t)B * sizeof(int32_t);            // seg_first / seg_last
-  bytes += kCtrlBytes;                                 // control block (chunk counter of the dynamic split)
   return (bytes + 255) & ~(size_t)255;
-}
-
-extern "C" int b200_decode_workspace_init(void* workspace, size_t workspace_bytes, b200_stream_t stream) {
-  using namespace b200;
-  if (!workspace || workspace_bytes < (size_t)kCtrlBytes) return fail("b200_decode_workspace_init: workspace < %d bytes", kCtrlBytes);
-  if ((uintptr_t)workspace & 15) return fail("b200_decode_workspace_init: workspace must be 16-byte aligned");
-  decode_ws_init_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((unsigned long long*)workspace);
-  return check_launch("b200_decode_workspace_init");
 }
 
 extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
@@ -612,12 +480,11 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   p.kv_indices = kv_indices;
   p.last_page_len = last_page_len;
   p.out = (__nv_bfloat16*)out;
-  const size_t parts = decode_parts(G, c, B);
-  p.part_o = (float*)((char*)workspace + kCtrlBytes);
+  const size_t parts = (size_t)G * c.subs + (size_t)B;
+  p.part_o = (float*)workspace;
   p.part_lse = p.part_o + parts * Hq * D;
   p.seg_first = (int32_t*)(p.part_lse + parts * Hq);
   p.seg_last = p.seg_first + B;
-  p.counter = decode_dynamic(c) ? (unsigned long long*)workspace : nullptr;
   p.q_row_stride = q_row_stride;
   p.out_row_stride = out_row_stride;
   p.kv_slot_stride = kv_slot_stride;
@@ -632,7 +499,7 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   cudaStream_t st = (cudaStream_t)stream;
   decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
   if (int rc = check_launch("b200_decode(stream)")) return rc;
-  cudaError_t e = launch_pdl(decode_merge_kernel, dim3(B, Hq), dim3(kMergeThreads), 0, st, p);
+  cudaError_t e = launch_pdl(decode_merge_kernel, dim3(B, Hq), dim3(128), 0, st, p);
   if (e != cudaSuccess) return fail("b200_decode(merge): %s", cudaGetErrorString(e));
   return check_launch("b200_decode(merge)");
 }

@@ -296,7 +296,6 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 constexpr int kItemRing = 4;
 constexpr int kPlanThreads = 1024;
 constexpr int kPlanBuckets = 1024;
-constexpr int kDecodeCtrlBytes = 64;    // control block of b200_decode at the start of a shared workspace: left untouched
 constexpr int kWorkHeaderInts = 16;     // [0] work counter, [1] number of (sequence, tile) pairs
 // Dynamic shared memory: 2 Q tiles + 4-slot K/V ring + one 32 KiB tile the softmax warps stage output rows in.
 constexpr int kWsOffStage = kWsOffRing + kRing * kTileBytes2;   // persistent kernel only
@@ -878,7 +877,7 @@ size_t prefill_sm100_workspace_bytes(int B, int total_q, int group) {
   while ((1 << log2_g) < group) ++log2_g;
   const int tok_per_cta = 2 * (kTM >> log2_g);
   const size_t max_pairs = (size_t)total_q / tok_per_cta + (size_t)B;
-  return kDecodeCtrlBytes + kWorkHeaderInts * sizeof(int) + max_pairs * sizeof(int2);
+  return kWorkHeaderInts * sizeof(int) + max_pairs * sizeof(int2);
 }
 
 int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, size_t workspace_bytes, cudaStream_t st) {
@@ -892,9 +891,9 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   static std::atomic<bool> attr_done[64];
   if (cudaError_t e = ensure_dyn_smem(prefill_sm100_persist_kernel, kPersistSmem, attr_done); e != cudaSuccess)
     return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-  int* work = reinterpret_cast<int*>(reinterpret_cast<char*>(workspace) + kDecodeCtrlBytes);   // b200_decode owns the first 64 bytes
+  int* work = reinterpret_cast<int*>(workspace);
   int2* items = reinterpret_cast<int2*>(work + kWorkHeaderInts);
-  const int max_pairs = (int)((workspace_bytes - kDecodeCtrlBytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
+  const int max_pairs = (int)((workspace_bytes - kWorkHeaderInts * sizeof(int)) / sizeof(int2));
   prefill_plan_kernel<<<1, kPlanThreads, 0, st>>>(p, 2 * tok_per_tile, work, items, max_pairs);
   if (int rc = check_launch("b200_prefill(plan)")) return rc;
   // Tensor maps (host-encoded per call: q and the layer's pool pointers change between calls; the maps travel as

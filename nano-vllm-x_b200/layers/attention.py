@@ -321,7 +321,7 @@ class AttentionBackend:
                                                self.head_dim))
         if self._workspace.numel() < need:
             # plans captured in CUDA graphs keep a reference to the buffer they were captured with
-            self._workspace = ops.decode_workspace_init(torch.empty(need, dtype=torch.uint8, device=self.device))
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self._workspace
 
     def _pages(self, n_tokens_total_upper: int, B: int) -> int:
@@ -376,9 +376,9 @@ class AttentionBackend:
         self._graph_scratch = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)
         self.slot_table.reserve(2 * max_bs, context_len)
         # one workspace, sized for the largest captured batch, shared by all graphs
-        self._graph_workspace = ops.decode_workspace_init(torch.empty(
+        self._graph_workspace = torch.empty(
             ops.decode_workspace_bytes(max_bs, self.num_qo_heads, self.num_kv_heads, self.head_dim),
-            dtype=torch.uint8, device=dev))
+            dtype=torch.uint8, device=dev)
         self._graph_context_len = context_len
 
     def build_metadata_for_cuda_graph_capture(self, graph, bs: int, context_len: int) -> AttentionMetadata:

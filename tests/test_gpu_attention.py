@@ -318,12 +318,10 @@ def test_decode_properties_long_context(pkg):
 
 
 @pytest.mark.parametrize("ps", [16, 1])
-def test_decode_dynamic_split_one_kv_head(pkg, ps):
-    """Ranks with ONE KV head and ~1.4 M tokens of context take the guided dynamic split (chunks claimed from the
-    counter in the workspace's control block).  Ragged lengths, every output row against a direct fp32 computation on
-    the device; the same workspace serves a prefill call in between and three decode calls (the counter is
-    re-armed by every call); repeated calls agree within tolerance (the order of claims is not deterministic, the
-    partials are merged in fp32)."""
+def test_decode_long_ragged_one_kv_head(pkg, ps):
+    """Ranks with ONE KV head (TP8 shapes: every warp is its own stream) and ~1.4 M tokens of ragged context: every
+    output row against a direct fp32 computation on the device; the same workspace serves a prefill call in between
+    and three decode calls, which must agree."""
     torch.manual_seed(1)
     rng = np.random.default_rng(3)
     B, Hq, Hkv, D = 48, 4, 1, 128
@@ -343,7 +341,7 @@ def test_decode_dynamic_split_one_kv_head(pkg, ps):
     outs = []
     for rep in range(3):
         outs.append(pkg.ops.decode(q, k_cache, v_cache, indptr, perm, last, ws, ps, sm).float())
-        if rep == 0:    # a prefill through the SAME workspace must leave the decode control block alone
+        if rep == 0:    # a prefill through the SAME workspace in between
             case = make_paged_case([300, 77], Hq, Hkv, q_lens=[300, 77], seed=4)
             d = dev(case)
             pkg.ops.prefill(d["q"], d["k_cache"], d["v_cache"], d["qo_indptr"], d["kv_indptr"], d["kv_indices"],
