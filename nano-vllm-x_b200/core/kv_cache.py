@@ -33,7 +33,7 @@ def store_kvcache(k: torch.Tensor, v: torch.Tensor, k_cache: torch.Tensor, v_cac
     assert kv_indices.numel() == num_tokens
     if kv_indices.dtype != torch.int64:
         kv_indices = kv_indices.to(torch.int64)
-    ops.store_kv(k, v, k_cache, v_cache, kv_indices.contiguous())
+    ops.call("store_kv", k, v, k_cache, v_cache, kv_indices.contiguous())
 
 
 class KVCachePool:

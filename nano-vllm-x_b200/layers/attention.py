@@ -64,9 +64,9 @@ class AttentionPlan:
         k_cache = k_cache.view(-1, self.num_kv_heads, self.head_dim)
         v_cache = v_cache.view(-1, self.num_kv_heads, self.head_dim)
         if self.mode == "DECODE":
-            return ops.decode(q, k_cache, v_cache, self.paged_kv_indptr, self.paged_kv_indices,
+            return ops.call("decode", q, k_cache, v_cache, self.paged_kv_indptr, self.paged_kv_indices,
                               self.paged_kv_last_page_len, self.workspace, self.page_size, self._sm_scale)
-        return ops.prefill(q, k_cache, v_cache, self.qo_indptr, self.paged_kv_indptr, self.paged_kv_indices,
+        return ops.call("prefill", q, k_cache, v_cache, self.qo_indptr, self.paged_kv_indptr, self.paged_kv_indices,
                            self.paged_kv_last_page_len, self.workspace, self.page_size, self._sm_scale, True)
 
 
@@ -218,10 +218,17 @@ class SlotTable:
         step = self.step
         B = len(seqs)
         row_of = self.row_of
-        rows = np.fromiter((row_of.get(s.seq_id, -1) for s in seqs), dtype=np.int64, count=B)
-        kvl = np.fromiter((len(s.kv_indices) for s in seqs), dtype=np.int64, count=B)
-        cach = np.fromiter((s.cached_kv_len for s in seqs), dtype=np.int64, count=B)
-        ntok = np.fromiter((len(s.token_ids) for s in seqs), dtype=np.int64, count=B)
+        # ONE pass over the Python objects: row, lengths and the three slots the O(1) checks need
+        # (first, last, and kv[cached_kv_len - 1]: the slot the fingerprint compares, since a trusted row has
+        # tracked == cached_kv_len)
+        def fields(q):
+            kv, c = q.kv_indices, q.cached_kv_len
+            n = len(kv)
+            return (row_of.get(q.seq_id, -1), n, c, len(q.token_ids), kv[0] if n else -1, kv[-1] if n else -1,
+                    kv[c - 1] if 0 < c <= n else -1)
+        arr = np.array([fields(q) for q in seqs], dtype=np.int64).reshape(B, 7)
+        rows, kvl, cach, ntok = arr[:, 0].copy(), arr[:, 1], arr[:, 2], arr[:, 3]
+        kv_first, kv_last, kv_prev = arr[:, 4], arr[:, 5], arr[:, 6]
         known = rows >= 0
         self.last_used[rows[known]] = step
         # O(1) fingerprint per known sequence
@@ -229,13 +236,7 @@ class SlotTable:
         if known.any():
             r = np.where(known, rows, 0)
             t = self.tracked[r]
-            trusted &= (t == cach) & (t > 0) & (kvl >= t)
-            idx = np.flatnonzero(trusted)
-            if idx.size:
-                f0 = np.fromiter((seqs[i].kv_indices[0] for i in idx), dtype=np.int64, count=idx.size)
-                fl = np.fromiter((seqs[i].kv_indices[int(t[i]) - 1] for i in idx), dtype=np.int64, count=idx.size)
-                ok = (f0 == self.first[r[idx]]) & (fl == self.last[r[idx]])
-                trusted[idx[~ok]] = False
+            trusted &= (t == cach) & (t > 0) & (kvl >= t) & (kv_first == self.first[r]) & (kv_prev == self.last[r])
         n_unknown = int(B - known.sum())
         if n_unknown:
             self._take_rows(n_unknown)
@@ -256,7 +257,7 @@ class SlotTable:
         n_payload = int(cnt.sum())
         payload = np.empty(n_payload, dtype=np.int32)
         if n_payload == B and bool((cnt == 1).all()):            # steady-state decode: one new slot per sequence
-            payload[:] = np.fromiter((s.kv_indices[-1] for s in seqs), dtype=np.int64, count=B)
+            payload[:] = kv_last
         else:
             for i in np.flatnonzero(cnt):
                 a, c = int(woff[i]), int(cnt[i])
@@ -264,7 +265,15 @@ class SlotTable:
                 payload[a:a + c] = kv if c == len(kv) else kv[len(kv) - c:]
         self.full_resends += int(((start == 0) & (kvl > 0)).sum())
         if page_size > 1 and n_payload:
-            self._check_pages(seqs, payload, start, cnt, woff, page_size)
+            if n_payload == B and bool(trusted.all()) and bool((cnt == 1).all()):
+                # steady-state decode, vectorised: the one new slot of every sequence either opens a page or follows
+                # the slot this table saw last (the fingerprint just verified that it is kv[start - 1])
+                head = start % page_size == 0
+                new = payload.astype(np.int64)
+                if not bool(np.all(np.where(head, new % page_size == 0, new == self.last[rows] + 1))):
+                    self._check_pages(seqs, payload, start, cnt, woff, page_size)     # raises with the sequence id
+            else:
+                self._check_pages(seqs, payload, start, cnt, woff, page_size)
         if self.verify:
             for i, s in enumerate(seqs):
                 mir = self._mirror.get(s.seq_id, [])
@@ -272,11 +281,11 @@ class SlotTable:
                 assert mir[:st] == list(s.kv_indices[:st]), f"slot table contract violated for seq {s.seq_id}"
                 self._mirror[s.seq_id] = list(s.kv_indices)
         # fingerprints for the next step
-        nz = np.flatnonzero(kvl > 0)
-        if nz.size:
+        nz = kvl > 0
+        if nz.any():
             rr = rows[nz]
-            self.first[rr] = np.fromiter((seqs[i].kv_indices[0] for i in nz), dtype=np.int64, count=nz.size)
-            self.last[rr] = np.fromiter((seqs[i].kv_indices[-1] for i in nz), dtype=np.int64, count=nz.size)
+            self.first[rr] = kv_first[nz]
+            self.last[rr] = kv_last[nz]
         self.tracked[rows] = kvl
         max_len = int(kvl.max()) if B else 0
         if max_len > self.table.shape[1]:      # (the copy of the old contents is ordered before this step's update)
@@ -350,7 +359,7 @@ class AttentionBackend:
         scratch, last_page_len = buf[n64 + 2 * nb:n64 + 2 * nb + B + 1], buf[n64 + 3 * nb:n64 + 3 * nb + B]
         kv_indices = buf[n64 + 4 * nb:n64 + 4 * nb + n_pages]
         if B > 0:
-            ops.step_meta(st.table, msg, B, n_payload, B, ps, False, qo_indptr, kv_indptr, kv_indices, last_page_len,
+            ops.call("step_meta", st.table, msg, B, n_payload, B, ps, False, qo_indptr, kv_indptr, kv_indices, last_page_len,
                           out_slots, scratch)
         else:
             qo_indptr.zero_()
@@ -408,7 +417,7 @@ class AttentionBackend:
         out_buf = graph.get_input_buffer("output_kv_indices_buffer")
         # the reference never rewrites last_page_len on replay (stays 1 at page_size 1); for
         # page_size > 1 it must be rebuilt
-        ops.step_meta(st.table, msg, bs, n_payload, padded_bs, self.page_size, True, None, indptr_buf, indices_buf,
+        ops.call("step_meta", st.table, msg, bs, n_payload, padded_bs, self.page_size, True, None, indptr_buf, indices_buf,
                       None if self.page_size == 1 else last_buf, out_buf, self._graph_scratch)
         plan = self._graph_plans[padded_bs]
         return AttentionMetadata(forward_mode=batch.forward_mode, kv_cache=self.kv_cache,
@@ -457,7 +466,7 @@ class Attention(nn.Module):
         qkv = qkv.view(-1, (Hq + 2 * Hkv) * D)
         k_cache, v_cache = md.kv_cache.get_kv_cache(self.layer_id)
         q = qkv[:, : Hq * D]
-        ops.qk_norm_rope_store(qkv, positions.reshape(-1), q_norm_weight, k_norm_weight, eps, cos_sin_cache, q, None,
+        ops.call("qk_norm_rope_store", qkv, positions.reshape(-1), q_norm_weight, k_norm_weight, eps, cos_sin_cache, q, None,
                                k_cache, v_cache, md.output_kv_indices, Hq, Hkv, D)
         return self.forward(q, None, None)
 

@@ -247,3 +247,17 @@ def launch_count() -> int:
 
 def reset_launch_count() -> None:
     _lib.load().b200_reset_launch_count()
+
+
+# ---- dispatcher-free calls for the layers ----------------------------------------------------------------
+# A torch.library custom op costs ~25 us of dispatcher work per call; a decode step issues three of them (step_meta,
+# store_kv, decode) and is itself 0.19 ms at the TP8 shapes.  Outside torch.compile tracing the layers therefore call
+# the ops' Python bodies directly (same checks, same C ABI call); under tracing the registered ops are used.
+_RAW = {n: getattr(globals()[n], "_init_fn", globals()[n])
+        for n in ("store_kv", "slot_table_update", "build_meta", "step_meta", "decode", "prefill", "qk_norm_rope_store", "sample")}
+
+
+def call(name: str, *args):
+    if torch.compiler.is_compiling():
+        return globals()[name](*args)
+    return _RAW[name](*args)
