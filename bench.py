@@ -571,6 +571,28 @@ def run_b200_arm(args):
         h_out = torch.empty((B, Hq * D), dtype=torch.bfloat16).pin_memory()
         d_qkv = torch.empty_like(qkv)
 
+        # The decode step of the reference engine is a CUDA-graph replay around build_metadata_for_cuda_graph_replay
+        # (core/model_runner.py:299-305, 332-417); the e2e leg drives the drop-in through that same public API:
+        # prepare_for_cuda_graph_capture -> build_metadata_for_cuda_graph_capture -> capture, then per step
+        # build_metadata_for_cuda_graph_replay + replay.  --no-graph uses the eager build_metadata path instead.
+        e2e_graph = None
+        static_out = torch.empty((B, Hq * D), dtype=torch.bfloat16, device=devc)
+
+        def fwd_static():
+            o = attn(d_qkv[:, :Hq * D], d_qkv[:, Hq * D:(Hq + Hkv) * D], d_qkv[:, (Hq + Hkv) * D:])
+            static_out.copy_(o)
+
+        if not args.no_graph:
+            e2e_graph = pkg.CUDAGraph()
+            ctx_cap = L + args.steps + max(args.warmup, 3) + 8
+            be.prepare_for_cuda_graph_capture(e2e_graph, B, ctx_cap)
+            md0 = be.build_metadata_for_cuda_graph_capture(e2e_graph, B, ctx_cap)
+            with pkg.attention_kv_cache(holder, md0):
+                fwd_static()
+                with e2e_graph.capture(B):
+                    fwd_static()
+            torch.cuda.synchronize()
+
         def step_e2e():
             # what the scheduler does between two decode steps (core/scheduler.py:119-128, 161-171): the token of the last
             # step is now cached, one more token and one more slot per sequence
@@ -581,10 +603,16 @@ def run_b200_arm(args):
                     sq.kv_indices.append(spare[i].pop())
             e2e_steps_done[0] += 1
             d_qkv.copy_(h_qkv, non_blocking=True)
-            md = be.build_metadata(batch)
-            with pkg.attention_kv_cache(holder, md):
-                o = attn(d_qkv[:, :Hq * D], d_qkv[:, Hq * D:(Hq + Hkv) * D], d_qkv[:, (Hq + Hkv) * D:])
-            h_out.copy_(o, non_blocking=True)
+            if e2e_graph is not None:
+                md = be.build_metadata_for_cuda_graph_replay(e2e_graph, batch, B)
+                with pkg.attention_kv_cache(holder, md):
+                    e2e_graph.replay(B)
+                h_out.copy_(static_out, non_blocking=True)
+            else:
+                md = be.build_metadata(batch)
+                with pkg.attention_kv_cache(holder, md):
+                    o = attn(d_qkv[:, :Hq * D], d_qkv[:, Hq * D:(Hq + Hkv) * D], d_qkv[:, (Hq + Hkv) * D:])
+                h_out.copy_(o, non_blocking=True)
             return be.slot_table.last_msg_bytes
 
         for _ in range(max(args.warmup, 3)):
@@ -607,7 +635,10 @@ def run_b200_arm(args):
         e2e = {"value": e2e_bytes * tp / (e2e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e2e_ms,
                "progression": f"real decode steps: context {L} -> {L + e2e_steps_done[0] - 1} tokens, one new slot per sequence per step",
                "h2d_bytes_per_step": int(h_qkv.numel() * 2 + msg_bytes), "d2h_bytes_per_step": int(h_out.numel() * 2),
-               "api": "AttentionBackend.build_metadata(host Sequence lists) + Attention.forward + output read-back"}
+               "api": ("AttentionBackend.build_metadata_for_cuda_graph_replay(host Sequence lists) + CUDAGraph.replay of "
+                       "Attention.forward (the reference's decode path, core/model_runner.py:299-305) + output read-back")
+               if e2e_graph is not None else
+               "AttentionBackend.build_metadata(host Sequence lists) + Attention.forward + output read-back"}
         torch.cuda.synchronize()
         sl_e = torch.tensor(seqs[b_chk].kv_indices, dtype=torch.long, device=devc)
         Ke, Ve = k_cache[sl_e, h_chk // (Hq // Hkv)].float(), v_cache[sl_e, h_chk // (Hq // Hkv)].float()
@@ -616,6 +647,7 @@ def run_b200_arm(args):
         e2e["self_check_max_abs_err"] = float((h_out.view(B, Hq, D)[b_chk, h_chk].to(devc).float() - ref_e).abs().max())
         e2e["full_resends_in_timed_steps"] = int(be.slot_table.full_resends - resends0)
         del be, attn, holder, seqs, batch, d_qkv
+        e2e_graph = static_out = None
 
     # ---- (C) CPU baseline (rank 0, N=1 only) -----------------------------------------------------------
     cpu = None

@@ -68,6 +68,10 @@ constexpr float kLazyTau = 8.0f;
 #define B200_PREFILL_PACKED 1
 #endif
 constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
+#ifndef B200_PREFILL_UNIMASK
+#define B200_PREFILL_UNIMASK 1
+#endif
+constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -93,7 +97,7 @@ __device__ __forceinline__ uint64_t add2_ordered(uint64_t a, uint64_t b) {
 template <bool MASK, int NCH = 4>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
                                              const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
-                                             const uint32_t bar_p1) {
+                                             const uint32_t bar_p1, const bool runtime_mask = false) {
   // NCH (masked tiles only, tile-uniform): number of 32-column chunks of S that hold any valid column of this
   // query tile.  The MMA issuer trims QK to N = 32*NCH and PV to K = 32*NCH, so chunks >= NCH are neither
   // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
@@ -108,6 +112,19 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 #pragma unroll
       for (int e = 0; e < 32; ++e)
         if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
+  } else if (runtime_mask) {
+    // kUnifiedMask: masked tiles (causal diagonal, ragged sequence end) set their invalid columns to -inf here and then
+    // run the SAME packed pipeline as the unmasked ones (exp2(-inf) = 0): one copy of the 450-instruction tile body
+    // instead of two (the kernel lives on instruction fetch: `no_inst` is 8-19 % of the softmax warps' stalls).  The
+    // branch is tile-uniform; the warp barrier inside keeps ptxas from if-converting the 256 compare / select pairs
+    // into predicated-off instructions of the common path.
+    sched_fence();
+#pragma unroll
+    for (int c = 0; c < NCH; ++c)
+#pragma unroll
+      for (int e = 0; e < 32; ++e)
+        if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
+    sched_fence();
   }
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
@@ -769,14 +786,11 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         tc_fence_after();
         const int kv0 = j * kTN;
         const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
-        if (need_mask) {
-          const int nvalid = min(lim, kv_hi - 1) - kv0 + 1;          // valid columns of my row in this tile
-          switch (chunks_of(kv_hi, j)) {                              // tile-uniform
-            case 1: softmax_tile<true, 1>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-            case 2: softmax_tile<true, 2>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-            case 3: softmax_tile<true, 3>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-            default: softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1)); break;
-          }
+        const int nvalid = need_mask ? min(lim, kv_hi - 1) - kv0 + 1 : kTN;   // valid columns of my row in this tile
+        if constexpr (kUnifiedMask) {
+          softmax_tile<false>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), need_mask);
+        } else if (need_mask) {
+          softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
         } else {
           softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
         }
