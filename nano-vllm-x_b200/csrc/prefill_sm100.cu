@@ -71,7 +71,11 @@ constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
 #ifndef B200_PREFILL_UNIMASK
 #define B200_PREFILL_UNIMASK 1
 #endif
-constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
+constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;
+#ifndef B200_PREFILL_SPLITLD
+#define B200_PREFILL_SPLITLD 0
+#endif
+constexpr bool kSplitLoad = B200_PREFILL_SPLITLD != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -103,39 +107,59 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
   static_assert(MASK || NCH == 4, "only masked tiles are trimmed");
   uint32_t sv[NCH][32];
-#pragma unroll
-  for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
-  tmem_wait_ld();
-  if (MASK) {
-#pragma unroll
-    for (int c = 0; c < NCH; ++c)
-#pragma unroll
-      for (int e = 0; e < 32; ++e)
-        if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
-  } else if (runtime_mask) {
-    // kUnifiedMask: masked tiles (causal diagonal, ragged sequence end) set their invalid columns to -inf here and then
-    // run the SAME packed pipeline as the unmasked ones (exp2(-inf) = 0): one copy of the 450-instruction tile body
-    // instead of two (the kernel lives on instruction fetch: `no_inst` is 8-19 % of the softmax warps' stalls).  The
-    // branch is tile-uniform; the warp barrier inside keeps ptxas from if-converting the 256 compare / select pairs
-    // into predicated-off instructions of the common path.
-    sched_fence();
-#pragma unroll
-    for (int c = 0; c < NCH; ++c)
-#pragma unroll
-      for (int e = 0; e < 32; ++e)
-        if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
-    sched_fence();
-  }
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+  // invalid columns -> -inf.  MASK: compile-time masked instance.  runtime_mask (kUnifiedMask): masked tiles (causal
+  // diagonal, ragged sequence end) mask here and then run the SAME packed pipeline as the unmasked ones (exp2(-inf) = 0):
+  // one copy of the 450-instruction tile body instead of two (the kernel lives on instruction fetch: `no_inst` is 8-19 %
+  // of the softmax warps' stalls).  The branch is tile-uniform; the warp barriers inside keep ptxas from if-converting
+  // the compare / select pairs into predicated-off instructions of the common path.
+  auto mask_chunks = [&](int c0, int c1) {
+    if (MASK) {
 #pragma unroll
-  for (int c = 0; c < NCH; ++c) {
+      for (int c = c0; c < c1; ++c)
 #pragma unroll
-    for (int e = 0; e < 32; e += 4) {
-      mx0 = fmaxf(mx0, __uint_as_float(sv[c][e]));
-      mx1 = fmaxf(mx1, __uint_as_float(sv[c][e + 1]));
-      mx2 = fmaxf(mx2, __uint_as_float(sv[c][e + 2]));
-      mx3 = fmaxf(mx3, __uint_as_float(sv[c][e + 3]));
+        for (int e = 0; e < 32; ++e)
+          if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
+    } else if (runtime_mask) {
+      sched_fence();
+#pragma unroll
+      for (int c = c0; c < c1; ++c)
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+          if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
+      sched_fence();
     }
+  };
+  auto max_chunks = [&](int c0, int c1) {
+#pragma unroll
+    for (int c = c0; c < c1; ++c) {
+#pragma unroll
+      for (int e = 0; e < 32; e += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(sv[c][e]));
+        mx1 = fmaxf(mx1, __uint_as_float(sv[c][e + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(sv[c][e + 2]));
+        mx3 = fmaxf(mx3, __uint_as_float(sv[c][e + 3]));
+      }
+    }
+  };
+  if constexpr (kSplitLoad && NCH == 4) {
+    // the row maximum of the first two chunks runs under the TMEM loads of the last two
+    tmem_ld_32x32b_x32(tS, sv[0]);
+    tmem_ld_32x32b_x32(tS + 32, sv[1]);
+    tmem_wait_ld();
+    tmem_ld_32x32b_x32(tS + 64, sv[2]);
+    tmem_ld_32x32b_x32(tS + 96, sv[3]);
+    mask_chunks(0, 2);
+    max_chunks(0, 2);
+    tmem_wait_ld();
+    mask_chunks(2, 4);
+    max_chunks(2, 4);
+  } else {
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+    tmem_wait_ld();
+    mask_chunks(0, NCH);
+    max_chunks(0, NCH);
   }
   const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2;   // scale > 0: max commutes
   float alpha = 1.f;
