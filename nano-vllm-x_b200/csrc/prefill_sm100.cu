@@ -72,10 +72,7 @@ constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
 #define B200_PREFILL_UNIMASK 1
 #endif
 constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;
-#ifndef B200_PREFILL_SPLITLD
-#define B200_PREFILL_SPLITLD 0
-#endif
-constexpr bool kSplitLoad = B200_PREFILL_SPLITLD != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
+   // masked tiles share the unmasked tile body (see softmax_tile)
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -142,25 +139,13 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       }
     }
   };
-  if constexpr (kSplitLoad && NCH == 4) {
-    // the row maximum of the first two chunks runs under the TMEM loads of the last two
-    tmem_ld_32x32b_x32(tS, sv[0]);
-    tmem_ld_32x32b_x32(tS + 32, sv[1]);
-    tmem_wait_ld();
-    tmem_ld_32x32b_x32(tS + 64, sv[2]);
-    tmem_ld_32x32b_x32(tS + 96, sv[3]);
-    mask_chunks(0, 2);
-    max_chunks(0, 2);
-    tmem_wait_ld();
-    mask_chunks(2, 4);
-    max_chunks(2, 4);
-  } else {
+  // (loading the chunks in two halves so that the maximum of the first runs under the loads of the second was
+  //  measured: -2..3 % on every shape, profiles/r2_s22_prefill_splitload_ab.txt)
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
-    tmem_wait_ld();
-    mask_chunks(0, NCH);
-    max_chunks(0, NCH);
-  }
+  for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+  tmem_wait_ld();
+  mask_chunks(0, NCH);
+  max_chunks(0, NCH);
   const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2;   // scale > 0: max commutes
   float alpha = 1.f;
   bool grow = false;
