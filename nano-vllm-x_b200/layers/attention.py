@@ -226,7 +226,13 @@ class SlotTable:
             n = len(kv)
             return (row_of.get(q.seq_id, -1), n, c, len(q.token_ids), kv[0] if n else -1, kv[-1] if n else -1,
                     kv[c - 1] if 0 < c <= n else -1)
-        arr = np.array([fields(q) for q in seqs], dtype=np.int64).reshape(B, 7)
+        get = row_of.get
+        try:      # common case inlined (no call per sequence): every sequence owns slots and 0 < cached_kv_len <= len(kv)
+            arr = np.array([(get(q.seq_id, -1), len(q.kv_indices), q.cached_kv_len, len(q.token_ids), q.kv_indices[0],
+                             q.kv_indices[-1], q.kv_indices[q.cached_kv_len - 1] if q.cached_kv_len > 0 else -1)
+                            for q in seqs], dtype=np.int64).reshape(B, 7)
+        except IndexError:
+            arr = np.array([fields(q) for q in seqs], dtype=np.int64).reshape(B, 7)
         rows, kvl, cach, ntok = arr[:, 0].copy(), arr[:, 1], arr[:, 2], arr[:, 3]
         kv_first, kv_last, kv_prev = arr[:, 4], arr[:, 5], arr[:, 6]
         known = rows >= 0
