@@ -71,16 +71,8 @@ constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
 #ifndef B200_PREFILL_UNIMASK
 #define B200_PREFILL_UNIMASK 1
 #endif
-constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
-// kEarlyHalfQK: S_t (128 fp32 columns) is free in its UPPER half as soon as the softmax group has pulled S_t(j) into
-// registers -- P_t(j) (bf16) only occupies columns [0, 64).  So the second half of QK_t(j+1) (KV tokens 64..127 ->
-// columns [64, 128), an N = 64 MMA group) is issued right then, under softmax(j); only the first half (columns
-// [0, 64)) has to wait for PV_t(j).  The chain softmax(j) -> PV(j) -> QK(j+1) -> softmax(j+1) of a query tile gets 256
-// clk shorter per KV tile, at the price of 16 instead of 8 QK MMAs per tile.
-#ifndef B200_PREFILL_EARLYB
-#define B200_PREFILL_EARLYB 0
-#endif
-constexpr bool kEarlyHalfQK = B200_PREFILL_EARLYB != 0;
+constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;
+   // masked tiles share the unmasked tile body (see softmax_tile)
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -106,8 +98,7 @@ __device__ __forceinline__ uint64_t add2_ordered(uint64_t a, uint64_t b) {
 template <bool MASK, int NCH = 4>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
                                              const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
-                                             const uint32_t bar_p1, const bool runtime_mask = false,
-                                             const uint32_t bar_sfree = 0) {
+                                             const uint32_t bar_p1, const bool runtime_mask = false) {
   // NCH (masked tiles only, tile-uniform): number of 32-column chunks of S that hold any valid column of this
   // query tile.  The MMA issuer trims QK to N = 32*NCH and PV to K = 32*NCH, so chunks >= NCH are neither
   // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
@@ -153,10 +144,6 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
 #pragma unroll
   for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
   tmem_wait_ld();
-  if constexpr (kEarlyHalfQK) {            // S_t is in registers: columns [64, 128) may take the next tile's scores
-    tc_fence_before();
-    mbar_arrive(bar_sfree);
-  }
   mask_chunks(0, NCH);
   max_chunks(0, NCH);
   const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2;   // scale > 0: max commutes
@@ -416,7 +403,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
                                                                                const __grid_constant__ CUtensorMap tm_v) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem;
-  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing + 2];
+  __shared__ __align__(8) uint64_t s_bar[2 + 2 * kRing + 8 + 2 * kItemRing];
   __shared__ __align__(16) ItemDesc s_items[kItemRing];
   __shared__ __align__(16) int s_slots[2][2][2][32];   // cp.async producers: [tile parity][warp][row parity][i]
 
@@ -447,7 +434,6 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   auto bar_o = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 6 + t); };
   auto bar_ifull = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + slot); };
   auto bar_iempty = [&](int slot) { return bar0 + 8u * (2 + 2 * kRing + 8 + kItemRing + slot); };
-  auto bar_sfree = [&](int t) { return bar0 + 8u * (2 + 2 * kRing + 8 + 2 * kItemRing + t); };   // S_t(j) is in registers
   constexpr int kItemConsumers = 11;   // 8 softmax warps + MMA warp + 2 TMA warps (lane 0 of each arrives)
 
   if (tid == 0) {
@@ -462,7 +448,6 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_init(bar_p(t, 0), 128);
       mbar_init(bar_p(t, 1), 128);
       mbar_init(bar_o(t), 1);
-      mbar_init(bar_sfree(t), 128);
     }
     for (int i = 0; i < kItemRing; ++i) {
       mbar_init(bar_ifull(i), 1);
@@ -735,95 +720,14 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           umma_ts_elect(tmem + 2 * kTN + t * kTD, tmem + t * kTN + ks * 8, vd + (uint64_t)(ks * (2048 >> 4)), idesc_pv,
                         (acc || ks > 0));
     };
-    // kEarlyHalfQK: one half (64 KV tokens -> 64 S columns) of QK_t; half 1 = tokens 64..127 -> columns [64, 128)
-    constexpr uint32_t idesc_qk64 = make_idesc_bf16_f32(kTM, 64, 0, 0);
-    auto issue_qk_half = [&](int t, int f, int half) {
-      const uint64_t qd = qdesc0 + (uint64_t)(t * (kTileBytes2 >> 4));
-      const uint64_t kd = kdesc0 + (uint64_t)((f % kRing) * (kTileBytes2 >> 4)) + (uint64_t)(half * (64 * 128 >> 4));
-#pragma unroll
-      for (int ks = 0; ks < kTD / 16; ++ks) {
-        const uint32_t koff = ((uint32_t)(ks >> 2) * kBlkBytes + (uint32_t)(ks & 3) * 32) >> 4;
-        umma_ss_elect(tmem + t * kTN + half * 64, qd + koff, kd + koff, idesc_qk64, ks > 0);
-      }
-    };
     int fillc = 0, qn = 0;
     int pc[2] = {0, 0};
-    int sfc[2] = {0, 0};          // kEarlyHalfQK: S tiles of group t whose "in registers" phase has been consumed
     for (int it = 0;; ++it) {
       const ItemDesc d = take_item(it);
       if (!d.valid) break;
       const ItemGeo g = item_geometry(d, tok_per_tile, p.causal);
       if (g.J == 0) continue;
       const int base = fillc;
-      if constexpr (kEarlyHalfQK) {
-        mbar_wait(bar_q, qn & 1);
-        mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int t = 0; t < 2; ++t)
-          if ((t ? g.nt1 : g.nt0) > 0) {
-            issue_qk_half(t, base, 0);
-            issue_qk_half(t, base, 1);
-            umma_commit_elect(bar_s(t));
-          }
-        umma_commit_elect(bar_empty(base % kRing));
-        if (g.J == 1) umma_commit_elect(bar_qfree);
-        for (int j = 0; j < g.J; ++j) {
-          const int fv = base + 2 * j + 1, fk = base + 2 * j + 2;
-          bool k_ready = false, v_ready = false;
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const int ntt = t ? g.nt1 : g.nt0;
-            // ---- upper half of the NEXT tile's scores, as soon as S_t(j) has left TMEM (non-blocking probe: if the
-            //      softmax group or K(j+1) is not there yet, the half is issued with the lower one below) ----------
-            bool upper_done = false;
-            if (j + 1 < ntt) {
-              if (!k_ready && mbar_test_wait(bar_full(fk % kRing), (fk / kRing) & 1)) k_ready = true;
-              if (k_ready && mbar_test_wait(bar_sfree(t), sfc[t] & 1)) {
-                ++sfc[t];
-                tc_fence_after();
-                issue_qk_half(t, fk, 1);
-                upper_done = true;
-              }
-            }
-            if (j < ntt) {
-              if (!v_ready) {
-                mbar_wait(bar_full(fv % kRing), (fv / kRing) & 1);         // V(j)
-                v_ready = true;
-              }
-              mbar_wait(bar_p(t, 0), pc[t] & 1);                           // first 64 columns of P_t(j) are in TMEM
-              tc_fence_after();
-              issue_pv(t, fv, 0, j > 0, 8);
-              mbar_wait(bar_p(t, 1), pc[t] & 1);                           // the rest
-              tc_fence_after();
-              issue_pv(t, fv, 1, true, 8);
-              ++pc[t];
-              if (j == ntt - 1) umma_commit_elect(bar_o(t));
-              if (!upper_done) {                 // consume this tile's "S in registers" phase (long complete: P is there)
-                mbar_wait(bar_sfree(t), sfc[t] & 1);
-                ++sfc[t];
-                tc_fence_after();
-              }
-            }
-            if (j + 1 < ntt) {
-              if (!k_ready) {
-                mbar_wait(bar_full(fk % kRing), (fk / kRing) & 1);         // K(j+1)
-                tc_fence_after();
-                k_ready = true;
-              }
-              if (!upper_done) issue_qk_half(t, fk, 1);
-              issue_qk_half(t, fk, 0);
-              umma_commit_elect(bar_s(t));
-            }
-          }
-          umma_commit_elect(bar_empty(fv % kRing));
-          if (j + 1 < g.J) umma_commit_elect(bar_empty(fk % kRing));
-          if (j + 2 == g.J) umma_commit_elect(bar_qfree);
-        }
-        fillc += 2 * g.J;
-        ++qn;
-        continue;
-      }
       mbar_wait(bar_q, qn & 1);
       mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
       tc_fence_after();
@@ -893,12 +797,11 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
         const int nvalid = need_mask ? min(lim, kv_hi - 1) - kv0 + 1 : kTN;   // valid columns of my row in this tile
         if constexpr (kUnifiedMask) {
-          softmax_tile<false>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), need_mask,
-                              bar_sfree(t));
+          softmax_tile<false>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), need_mask);
         } else if (need_mask) {
-          softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), false, bar_sfree(t));
+          softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
         } else {
-          softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), false, bar_sfree(t));
+          softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
         }
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
