@@ -8,13 +8,16 @@ pages (fragmented), Hq/Hkv = 32/8 at TP1 and 32/N / 8/N per rank at TP N (KV-hea
 collective on the path).  One "step" = one decode pass of the hot path over the
 batch: slot write of the 64 new K/V rows + split-KV paged decode attention (+ merge).
 
-  value     algorithmic GB/s (SURVEY.md 8d formula) with everything resident in HBM, whole step
-  e2e       same metric through the public drop-in API (AttentionBackend.build_metadata from host
-            Sequence lists -> Attention.forward) with q/k/v in pinned HOST memory and the output
-            read back to the host every step
-  roofline  the dominant kernel (decode streaming kernel + its merge) timed alone with CUDA events
-  cpu_baseline  the oracle's fp32 torch restatement of the reference semantics on the host cores,
-            on a bounded sample (a few sequences of the same workload)
+  value     algorithmic GB/s (SURVEY.md 8d formula) with everything resident in HBM, whole step, K CUDA-graph replays
+  e2e       same metric through the public drop-in API with q/k/v in pinned HOST memory and the output read back to the
+            host every step: a real decode progression (one new token and slot per sequence per step) driven as the
+            reference drives decode -- AttentionBackend.build_metadata_for_cuda_graph_replay (host Sequence lists) +
+            replay of the captured Attention.forward (core/model_runner.py:299-305); --no-graph: eager build_metadata
+  roofline  the dominant kernel (decode streaming kernel + its merge): its share of the step from a paired pass
+            (step graph / decode-only graph replayed alternately) applied to the timed ms_per_step
+  cpu_baseline  the oracle's plain-C port of the reference semantics on the host cores, on the whole workload
+  prefill / gpu_reference / engine   extra keys: tensor-pipe roofline of the prefill kernel, FlashInfer on the same
+            inputs, the STOCK reference engine (baseline/_ref) with and without the drop-in at tp = N
 
 `--impl reference` times that CPU restatement only (the reference has no CPU attention of its own:
 FlashInfer and Triton are CUDA-only) and prints the same JSON line shape.
