@@ -71,8 +71,14 @@ constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
 #ifndef B200_PREFILL_UNIMASK
 #define B200_PREFILL_UNIMASK 1
 #endif
-constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;
-   // masked tiles share the unmasked tile body (see softmax_tile)
+constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
+// kLeanEpilogue: output-row addresses as one 64-bit base per item + 32-bit deltas per store, 1/l scaling with packed
+// FMUL2.  On bench-shaped prompts (1..8 KV tiles per item) the epilogue was 28 % of the softmax warps' time, most of it
+// 64-bit address arithmetic of the 16 stores per thread (profiles/r2s22_tree_prefill_short_roles.txt).
+#ifndef B200_PREFILL_LEANEPI
+#define B200_PREFILL_LEANEPI 1
+#endif
+constexpr bool kLeanEpilogue = B200_PREFILL_LEANEPI != 0;
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -84,6 +90,11 @@ __device__ __forceinline__ void unpack2(uint64_t v, uint32_t& lo, uint32_t& hi) 
 __device__ __forceinline__ uint64_t fma2_ordered(uint64_t a, uint64_t b, uint64_t c) {
   uint64_t r;
   asm volatile("fma.rn.f32x2 %0, %1, %2, %3;\n" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
 __device__ __forceinline__ uint64_t add2_ordered(uint64_t a, uint64_t b) {
@@ -853,8 +864,52 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           }
         }
       }
+      if (kLeanEpilogue && has && staged) {
+        // one 64-bit base per item (first token of this query tile, first head of the KV head's group, this lane's
+        // 16-byte piece); per store a 32-bit element delta from the packed row index R = (token, head-in-group)
+        __nv_bfloat16* const out0 = p.out + (int64_t)(d.q0 + d.j0 + t * tok_per_tile) * p.out_row_stride +
+                                    (int64_t)(d.kvh * G) * kTD + piece * 8;
+        const uint32_t stride32 = (uint32_t)p.out_row_stride;
+        const int R0 = (warp & 3) * 32 + rsub;
+        const uint64_t inv2 = pack2(__float_as_uint(inv_l), __float_as_uint(inv_l));
 #pragma unroll
-      for (int half = 0; half < 2 && has && staged; ++half) {
+        for (int half = 0; half < 2; ++half) {
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            uint32_t ov[32];
+            tmem_ld_32x32b_x32(tO + (half * 2 + cc) * 32, ov);
+            tmem_wait_ld();
+#pragma unroll
+            for (int j8 = 0; j8 < 4; ++j8) {
+              uint32_t w[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint32_t lo, hi;
+                unpack2(mul2(pack2(ov[j8 * 8 + 2 * q], ov[j8 * 8 + 2 * q + 1]), inv2), lo, hi);
+                w[q] = pack_bf16x2(__uint_as_float(lo), __uint_as_float(hi));
+              }
+              const uint32_t dst_s = stage + (uint32_t)lane * 128u + (uint32_t)(((cc * 4 + j8) ^ (lane & 7)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst_s), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+            }
+          }
+          __syncwarp();
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int row = 4 * k + rsub;                  // row of this warp's 32
+            uint4 w;
+            const uint32_t src_s = stage + (uint32_t)row * 128u + (uint32_t)((piece ^ (row & 7)) << 4);
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];\n" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(src_s) : "memory");
+            const int R = R0 + 4 * k;                      // packed row of tile t
+            if (R < rows_ok) {
+              const uint32_t delta = (uint32_t)(R >> log2_g) * stride32 + (uint32_t)(R & (G - 1)) * kTD + half * 64;
+              *reinterpret_cast<uint4*>(out0 + delta) = w;
+            }
+          }
+          __syncwarp();                                    // the next half (or item) overwrites the staging rows
+        }
+      }
+#pragma unroll
+      for (int half = 0; half < 2 && has && staged && !kLeanEpilogue; ++half) {
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
           uint32_t ov[32];
@@ -911,6 +966,7 @@ int launch_prefill_sm100(const PrefillParams& p, int total_q, void* workspace, s
   const size_t need = prefill_sm100_workspace_bytes(p.B, total_q, p.group);
   if (!workspace || workspace_bytes < need) return fail("b200_prefill: workspace %zu < %zu bytes", workspace_bytes, need);
   if ((uintptr_t)workspace & 15) return fail("b200_prefill: workspace must be 16-byte aligned");
+  if (p.out_row_stride < 0 || p.out_row_stride > (1 << 22)) return fail("b200_prefill: out row stride %lld not in [0, 2^22]", (long long)p.out_row_stride);
   static std::atomic<bool> attr_done[64];
   if (cudaError_t e = ensure_dyn_smem(prefill_sm100_persist_kernel, kPersistSmem, attr_done); e != cudaSuccess)
     return fail("b200_prefill(sm100 persist): cudaFuncSetAttribute: %s", cudaGetErrorString(e));
