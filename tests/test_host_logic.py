@@ -174,3 +174,32 @@ def test_cuda_graph_registry(pkg):
     assert g.get_input_buffer("x") is t and not g.is_captured
     g.captured_bs, g.max_bs, g.graphs = [1, 2, 4, 8], 8, {1: 0, 2: 0, 4: 0, 8: 0}
     assert [g.match_bs(b) for b in (1, 2, 3, 4, 5, 8)] == [1, 2, 4, 4, 8, 8]   # core/cuda_graph.py:44-47
+
+
+def test_pack_step_degenerate_sequences_and_page_run_check(pkg):
+    """The single-pass field extraction has an inlined fast path; sequences it cannot index (no slots yet,
+    cached_kv_len beyond the slots) must fall back to the guarded form and produce the same message; the vectorised
+    page-run check of steady-state decode must still raise on a slot that neither opens a page nor follows its
+    predecessor."""
+    import pytest
+    st = pkg.SlotTable(torch.device("cpu"), rows=4, cols=64)
+    table = st.table.numpy()
+    a, b, c = S("a", 6, range(100, 106), 0), S("b", 0, [], 0), S("c", 3, range(200, 203), 0)
+    msg, n_payload, total_q, total_kv, total_new = st.pack_step([a, b, c], 1)
+    apply_update(table, msg, 3, n_payload)
+    m = model_build_meta(table, msg, 3, 1)
+    ref = orc.build_metadata([orc.SeqView(6, list(range(100, 106)), 0), orc.SeqView(0, [], 0), orc.SeqView(3, [200, 201, 202], 0)])
+    assert np.array_equal(m.paged_kv_indices, ref.paged_kv_indices) and np.array_equal(m.paged_kv_indptr, ref.paged_kv_indptr)
+    assert (total_q, total_kv, total_new) == (9, 9, 9)
+    # steady-state decode at page_size 4: slots must be page-aligned runs
+    st4 = pkg.SlotTable(torch.device("cpu"), rows=4, cols=64)
+    seqs = [S("x", 7, range(40, 47), 0), S("y", 4, range(80, 84), 0)]
+    st4.pack_step(seqs, 4)
+    for s_, nxt in zip(seqs, (47, 120)):          # x continues its page, y opens a new, aligned page
+        s_.cached_kv_len = len(s_.kv_indices); s_.token_ids.append(0); s_.kv_indices.append(nxt)
+    msg, n_payload, *_ = st4.pack_step(seqs, 4)
+    assert n_payload == 2 and st4.full_resends == 2
+    for s_, nxt in zip(seqs, (48, 122)):          # y's new slot is neither aligned nor consecutive
+        s_.cached_kv_len = len(s_.kv_indices); s_.token_ids.append(0); s_.kv_indices.append(nxt)
+    with pytest.raises(ValueError, match="page-aligned"):
+        st4.pack_step(seqs, 4)
