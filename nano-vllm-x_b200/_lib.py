@@ -27,8 +27,6 @@ SIGNATURES = {
     "b200_build_meta": (_i32, [_vp, _i64, _vp, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _i64, _vp, _vp,
                                _i64, _vp, _vp]),
     "b200_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
-    "b200_decode_workspace_state_bytes": (_sz, []),
-    "b200_decode_workspace_init": (_i32, [_vp, _sz, _vp]),
     "b200_decode": (_i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i32, _i32,
                            _i32, _i32, _i32, _f32, _i32, _vp]),
     "b200_prefill_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),

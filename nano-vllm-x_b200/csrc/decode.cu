@@ -25,12 +25,7 @@
 //    HBM-bound, tensor throughput is irrelevant here, the point is ~10x fewer issue slots than
 //    an FMA formulation.  Online softmax in fp32 with quad shuffles (exp2 domain).
 //  * Segments that cover a whole sequence write bf16 output directly; the rest write fp32
-//    partials + log-sum-exp to the workspace and take a ticket on a per-(sequence, KV head)
-//    counter: the LAST arriver merges the partials of that pair and writes the output row
-//    (threadfence + atomic ticket, partials read back with ld.cg), then resets the counter.
-//    ONE launch per call; the separate merge kernel of rounds 1-2 cost 7-8 us per step, a fifth of
-//    a short decode batch at one KV head per rank.  The counters live in a control block at the
-//    start of the workspace that survives between calls (b200_decode_workspace_init).
+//    partials + log-sum-exp to the workspace and a small merge kernel (PDL) combines them.
 //
 // Algorithmic bytes per call: sum_i 2*Lkv_i*Hkv*D*2 + 2*B*Hq*D*2 + index bytes.
 #include "common.cuh"
@@ -48,10 +43,6 @@ constexpr int kWarpSmem = kStages * kStageBytes;       // 24 KiB
 constexpr int kDecodeSmem = kWarps * kWarpSmem;        // 192 KiB
 constexpr int kMinTilesPerStream = 2;  // do not split finer than 32 tokens per stream
 constexpr int kMaxSmemSeqs = 4096;     // batches up to this size keep their tile prefix in shared memory
-constexpr uint32_t kCtrlMagic = 0xB200DEC1u;          // first word of an initialised workspace
-constexpr int kCtrlBytes = 64;                        // control block
-constexpr int kMaxTickets = 65536;                    // (sequence, KV head) counters: B * Hkv <= 65536
-constexpr size_t kStateBytes = kCtrlBytes + (size_t)kMaxTickets * sizeof(int32_t);   // what survives between calls
 
 struct DecodeParams {
   const __nv_bfloat16* q;
@@ -63,8 +54,8 @@ struct DecodeParams {
   __nv_bfloat16* out;
   float* part_o;      // [G*subs+B][Hq][D]
   float* part_lse;    // [G*subs+B][Hq]
-  const uint32_t* ctrl;   // control block: [0] = kCtrlMagic once b200_decode_workspace_init has run
-  int32_t* tickets;   // [B * Hkv] arrivals per (sequence, KV head); zero between calls
+  int32_t* seg_first; // [B]
+  int32_t* seg_last;  // [B]
   int64_t q_row_stride, out_row_stride, kv_slot_stride;
   int B, Hq, Hkv, group, log2_ps;
   int heads_per_cta;  // KV heads handled by one CTA (<= 8)
@@ -76,54 +67,6 @@ __device__ __forceinline__ int tiles_of(const DecodeParams& p, int i) {
   return (seq_kv_len(p.kv_indptr, p.last_page_len, i, p.log2_ps) + kTile - 1) / kTile;
 }
 
-// Merge of the n partials [first, first + n) of (sequence s, KV head): run by the warp that arrived last on the pair's
-// ticket.  Per query head of the group: the log-sum-exps are read lane-parallel (32 partials per round trip), their
-// maximum by shuffles, then the partial rows with 8 independent 512-byte loads in flight, a lane owning 4 output dims.
-// ld.cg: the partials were written by other SMs, L1 must not serve them.
-__device__ __noinline__ void merge_partials(const DecodeParams& p, const int s, const int kv_head, const int first, const int n,
-                                            const int lane) {
-  for (int g = 0; g < p.group; ++g) {
-    const int hq = kv_head * p.group + g;
-    const float* lse = p.part_lse + (int64_t)first * p.Hq + hq;
-    const float4* po = reinterpret_cast<const float4*>(p.part_o + ((int64_t)first * p.Hq + hq) * kD) + lane;
-    const int64_t po_stride = (int64_t)p.Hq * kD / 4;
-    float M = -INFINITY, W = 0.f;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int base = 0; base < n; base += 32) {
-      const int i = base + lane;
-      const float l = i < n ? __ldcg(lse + (int64_t)i * p.Hq) : -INFINITY;
-      float mc = l;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) mc = fmaxf(mc, __shfl_xor_sync(0xffffffffu, mc, o));
-      const float Mn = fmaxf(M, mc);
-      if (Mn == -INFINITY) continue;                       // nothing but empty partials so far (warp-uniform)
-      const float sc = M == -INFINITY ? 0.f : fast_exp2(M - Mn);
-      acc.x *= sc; acc.y *= sc; acc.z *= sc; acc.w *= sc;
-      W *= sc;
-      M = Mn;
-      const float w_lane = l == -INFINITY ? 0.f : fast_exp2(l - Mn);
-      const int cnt = min(32, n - base);
-      for (int j0 = 0; j0 < cnt; j0 += 8) {
-        float4 v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          v[u] = j0 + u < cnt ? __ldcg(po + (int64_t)(base + j0 + u) * po_stride) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float w = __shfl_sync(0xffffffffu, w_lane, (j0 + u) & 31);   // lanes >= cnt hold 0
-          W += w;
-          acc.x += w * v[u].x; acc.y += w * v[u].y; acc.z += w * v[u].z; acc.w += w * v[u].w;
-        }
-      }
-    }
-    const float inv = W > 0.f ? 1.f / W : 0.f;
-    uint2 o2;
-    o2.x = pack_bf16x2(acc.x * inv, acc.y * inv);
-    o2.y = pack_bf16x2(acc.z * inv, acc.w * inv);
-    *reinterpret_cast<uint2*>(p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD + lane * 4) = o2;
-  }
-}
-
 __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodeParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ int s_scan[kWarps + 1];
@@ -132,6 +75,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = gridDim.x;
   const int head_group = blockIdx.y;  // which block of heads_per_cta KV heads
+  griddep_launch_dependents();        // the merge grid may become resident now; it waits for this grid to finish
 
   // ---- device-side schedule: one scan of the batch's tile counts ------------------------------
   const bool in_smem = p.B <= kMaxSmemSeqs;
@@ -145,18 +89,6 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
     total += blk;
   }
   __syncthreads();   // the last block-wide barrier of this kernel
-  if (tid == 0 && *p.ctrl != kCtrlMagic) __trap();   // workspace never went through b200_decode_workspace_init (or was
-                                                     // overwritten by another kernel between calls)
-  // sequences without any KV produce zero rows (one CTA; rare)
-  if (blockIdx.x == 0 && head_group == 0) {
-    for (int i = warp; i < p.B; i += kWarps) {
-      const int nt_i = in_smem ? s_incl[i] - (i ? s_incl[i - 1] : 0) : tiles_of(p, i);
-      if (nt_i == 0) {
-        uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)i * p.out_row_stride);
-        for (int e = lane; e < p.Hq * kD / 8; e += 32) dst[e] = make_uint4(0u, 0u, 0u, 0u);
-      }
-    }
-  }
 
   const int hh = warp % p.heads_per_cta;           // KV head inside the CTA's head block
   const int sub = warp / p.heads_per_cta;          // stream of this CTA
@@ -396,45 +328,86 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_kernel(const DecodePara
     const int seg_e = min(t_end, cpre + cnt) - cpre;
     if (tile + 1 == seg_e) {
       const int seg_b = max(t_begin, cpre) - cpre;
+      const int slot_id = k_stream + cs;     // unique per (stream, sequence) segment, see header
       const bool whole = (seg_b == 0) && (seg_e == cnt);
+      if (lane == 0 && hh == 0 && head_group == 0) {
+        if (seg_b == 0) p.seg_first[cs] = slot_id;
+        if (seg_e == cnt) p.seg_last[cs] = slot_id;
+      }
       float l_tot = l_run + __shfl_xor_sync(0xffffffffu, l_run, 1);
       l_tot += __shfl_xor_sync(0xffffffffu, l_tot, 2);
-      const float inv_l = l_tot > 0.f ? 1.f / l_tot : 0.f;
-      const int hq = kv_head * p.group + row;
-      if (whole) {
-        if (row_real) {
+      if (row_real) {
+        const float inv_l = l_tot > 0.f ? 1.f / l_tot : 0.f;
+        const int hq = kv_head * p.group + row;
+        if (whole) {
           __nv_bfloat16* dst = p.out + (int64_t)cs * p.out_row_stride + (int64_t)hq * kD + quad * 2;
 #pragma unroll
           for (int j = 0; j < kD / 8; ++j)
             *reinterpret_cast<uint32_t*>(dst + j * 8) = pack_bf16x2(o[j][0] * inv_l, o[j][1] * inv_l);
-        }
-      } else {
-        // the streams that hold a piece of this sequence: [k_first, k_last]; partial slot = stream + sequence
-        const int k_first = cpre / per, k_last = (cpre + cnt - 1) / per;
-        const int slot_id = k_stream + cs;
-        if (row_real) {
+        } else {
           float* dst = p.part_o + ((int64_t)slot_id * p.Hq + hq) * kD + quad * 2;
 #pragma unroll
           for (int j = 0; j < kD / 8; ++j)
             *reinterpret_cast<float2*>(dst + j * 8) = make_float2(o[j][0] * inv_l, o[j][1] * inv_l);
           if (quad == 0) p.part_lse[(int64_t)slot_id * p.Hq + hq] = l_tot > 0.f ? m_run + fast_log2(l_tot) : -INFINITY;
         }
-        // ticket: every lane's stores are device-visible before lane 0 arrives; the last arriver sees all partials
-        __threadfence();
-        __syncwarp();
-        int old = 0;
-        int32_t* ticket = p.tickets + (int64_t)cs * p.Hkv + kv_head;
-        if (lane == 0) old = atomicAdd(ticket, 1);
-        old = __shfl_sync(0xffffffffu, old, 0);
-        if (old == k_last - k_first) {
-          __threadfence();
-          merge_partials(p, cs, kv_head, k_first + cs, k_last - k_first + 1, lane);
-          if (lane == 0) *ticket = 0;              // re-armed for the next call
-        }
       }
     }
   }
   cp_async_wait<0>();
+}
+
+// Merge pass: one CTA per (sequence, query head); 4 warps split the partial list, a lane owns 4 output
+// dims (float4 loads: one coalesced 512-byte row per partial per warp), warps combine through smem.
+__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeParams p) {
+  const int s = blockIdx.x, hq = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __nv_bfloat16* dst = p.out + (int64_t)s * p.out_row_stride + (int64_t)hq * kD;
+  griddep_wait();                     // launched with PDL: partials / segment maps come from decode_kernel
+  const int L = seq_kv_len(p.kv_indptr, p.last_page_len, s, p.log2_ps);
+  if (L == 0) {
+    dst[threadIdx.x] = __float2bfloat16(0.f);
+    return;
+  }
+  const int first = p.seg_first[s], last = p.seg_last[s];
+  if (first == last) return;  // one segment: written directly by the streaming kernel
+  const int n = last - first + 1;
+  const float* lse = p.part_lse + (int64_t)first * p.Hq + hq;
+  const float4* po = reinterpret_cast<const float4*>(p.part_o + ((int64_t)first * p.Hq + hq) * kD) + lane;
+  const int64_t po_stride = (int64_t)p.Hq * kD / 4;
+  __shared__ float s_m[4], s_w[4];
+  __shared__ float4 s_acc[4][32];
+  float mx = -INFINITY;
+  for (int i = warp; i < n; i += 4) mx = fmaxf(mx, lse[(int64_t)i * p.Hq]);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  float wsum = 0.f;
+#pragma unroll 4
+  for (int i = warp; i < n; i += 4) {
+    const float l = lse[(int64_t)i * p.Hq];
+    const float w = l == -INFINITY ? 0.f : fast_exp2(l - mx);
+    const float4 v = po[(int64_t)i * po_stride];
+    wsum += w;
+    acc.x += w * v.x; acc.y += w * v.y; acc.z += w * v.z; acc.w += w * v.w;
+  }
+  if (lane == 0) { s_m[warp] = mx; s_w[warp] = wsum; }
+  s_acc[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0) {
+    const float M = fmaxf(fmaxf(s_m[0], s_m[1]), fmaxf(s_m[2], s_m[3]));
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    float W = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float f = s_m[w] == -INFINITY ? 0.f : fast_exp2(s_m[w] - M);
+      const float4 a = s_acc[w][lane];
+      W += f * s_w[w];
+      r.x += f * a.x; r.y += f * a.y; r.z += f * a.z; r.w += f * a.w;
+    }
+    const float inv = W > 0.f ? 1.f / W : 0.f;
+    uint2 o2;
+    o2.x = pack_bf16x2(r.x * inv, r.y * inv);
+    o2.y = pack_bf16x2(r.z * inv, r.w * inv);
+    *reinterpret_cast<uint2*>(dst + lane * 4) = o2;
+  }
 }
 
 static int ilog2_exact_d(int x) {
@@ -466,30 +439,10 @@ extern "C" size_t b200_decode_workspace_bytes(int32_t B, int32_t Hq, int32_t Hkv
   if (B <= 0 || Hq <= 0 || D <= 0 || !decode_cfg(Hkv, &c)) return 0;
   const int G = cached_num_sms();
   const size_t parts = (size_t)G * c.subs + (size_t)B;
-  size_t bytes = kStateBytes;                          // control block + tickets (survive between calls)
-  bytes += parts * Hq * D * sizeof(float);             // part_o
+  size_t bytes = parts * Hq * D * sizeof(float);       // part_o
   bytes += parts * Hq * sizeof(float);                 // part_lse
+  bytes += 2 * (size_t)B * sizeof(int32_t);            // seg_first / seg_last
   return (bytes + 255) & ~(size_t)255;
-}
-
-namespace b200 {
-__global__ void decode_ws_init_kernel(uint32_t* ctrl) {
-  if (threadIdx.x == 0) ctrl[0] = kCtrlMagic;
-}
-}  // namespace b200
-
-extern "C" size_t b200_decode_workspace_state_bytes(void) { return b200::kStateBytes; }
-
-extern "C" int b200_decode_workspace_init(void* workspace, size_t workspace_bytes, b200_stream_t stream) {
-  using namespace b200;
-  if (!workspace || workspace_bytes < kStateBytes)
-    return fail("b200_decode_workspace_init: workspace %zu < %zu bytes", workspace_bytes, kStateBytes);
-  if ((uintptr_t)workspace & 15) return fail("b200_decode_workspace_init: workspace must be 16-byte aligned");
-  cudaStream_t st = (cudaStream_t)stream;
-  if (cudaError_t e = cudaMemsetAsync(workspace, 0, kStateBytes, st); e != cudaSuccess)
-    return fail("b200_decode_workspace_init: cudaMemsetAsync: %s", cudaGetErrorString(e));
-  decode_ws_init_kernel<<<1, 32, 0, st>>>((uint32_t*)workspace);
-  return check_launch("b200_decode_workspace_init");
 }
 
 extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
@@ -515,7 +468,6 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
     return fail("b200_decode: k_cache / v_cache / workspace must be 16-byte aligned");
   if (((uintptr_t)q & 3) || (q_row_stride & 1)) return fail("b200_decode: q must be 4-byte aligned");
   if (((uintptr_t)out & 7) || (out_row_stride & 3)) return fail("b200_decode: out must be 8-byte aligned");
-  if ((int64_t)B * Hkv > kMaxTickets) return fail("b200_decode: B * Hkv = %lld > %d not built", (long long)B * Hkv, kMaxTickets);
   const size_t need = b200_decode_workspace_bytes(B, Hq, Hkv, D);
   if (workspace_bytes < need) return fail("b200_decode: workspace %zu < %zu bytes", workspace_bytes, need);
 
@@ -529,10 +481,10 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
   p.last_page_len = last_page_len;
   p.out = (__nv_bfloat16*)out;
   const size_t parts = (size_t)G * c.subs + (size_t)B;
-  p.ctrl = (const uint32_t*)workspace;
-  p.tickets = (int32_t*)((char*)workspace + kCtrlBytes);
-  p.part_o = (float*)((char*)workspace + kStateBytes);
+  p.part_o = (float*)workspace;
   p.part_lse = p.part_o + parts * Hq * D;
+  p.seg_first = (int32_t*)(p.part_lse + parts * Hq);
+  p.seg_last = p.seg_first + B;
   p.q_row_stride = q_row_stride;
   p.out_row_stride = out_row_stride;
   p.kv_slot_stride = kv_slot_stride;
@@ -546,5 +498,8 @@ extern "C" int b200_decode(const void* q, int64_t q_row_stride, const void* k_ca
     return fail("b200_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   cudaStream_t st = (cudaStream_t)stream;
   decode_kernel<<<dim3(G, c.head_groups), kWarps * 32, kDecodeSmem, st>>>(p);
-  return check_launch("b200_decode");
+  if (int rc = check_launch("b200_decode(stream)")) return rc;
+  cudaError_t e = launch_pdl(decode_merge_kernel, dim3(B, Hq), dim3(128), 0, st, p);
+  if (e != cudaSuccess) return fail("b200_decode(merge): %s", cudaGetErrorString(e));
+  return check_launch("b200_decode(merge)");
 }

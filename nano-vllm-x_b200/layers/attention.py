@@ -325,23 +325,17 @@ class AttentionBackend:
         if self.device.type != "cuda":
             raise RuntimeError("AttentionBackend needs a CUDA device: the b200attn path has no CPU fallback")
         self.slot_table = SlotTable(self.device)
-        self._workspace = torch.empty(0, dtype=torch.uint8, device=self.device)          # prefill work list
-        self._decode_workspace = torch.empty(0, dtype=torch.uint8, device=self.device)   # decode partials + state
+        self._workspace = torch.empty(0, dtype=torch.uint8, device=self.device)
         self._graph_plans: dict[int, AttentionPlan] = {}
         self._graph_scratch: Optional[torch.Tensor] = None
 
     # -- helpers -----------------------------------------------------------------------------------
-    def _ensure_workspace(self, mode: str, bs: int, total_q: int) -> torch.Tensor:
-        """Decode and prefill keep SEPARATE buffers: the decode workspace carries state between calls (the arrival
-        counters of the in-kernel merge, include/b200attn.h) and must not be written by anybody else."""
-        if mode == "DECODE":
-            need = ops.decode_workspace_bytes(max(bs, 1), self.num_qo_heads, self.num_kv_heads, self.head_dim)
-            if self._decode_workspace.numel() < need:
-                # plans captured in CUDA graphs keep a reference to the buffer they were captured with
-                self._decode_workspace = ops.decode_workspace_init(torch.empty(need, dtype=torch.uint8, device=self.device))
-            return self._decode_workspace
-        need = ops.prefill_workspace_bytes(max(bs, 1), max(total_q, 1), self.num_qo_heads, self.num_kv_heads, self.head_dim)
+    def _ensure_workspace(self, bs: int, total_q: int) -> torch.Tensor:
+        need = max(ops.decode_workspace_bytes(max(bs, 1), self.num_qo_heads, self.num_kv_heads, self.head_dim),
+                   ops.prefill_workspace_bytes(max(bs, 1), max(total_q, 1), self.num_qo_heads, self.num_kv_heads,
+                                               self.head_dim))
         if self._workspace.numel() < need:
+            # plans captured in CUDA graphs keep a reference to the buffer they were captured with
             self._workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self._workspace
 
@@ -377,7 +371,7 @@ class AttentionBackend:
             qo_indptr.zero_()
             kv_indptr.zero_()
         plan = AttentionPlan(mode, B, total_q, ps, qo_indptr, kv_indptr, kv_indices, last_page_len,
-                             self._ensure_workspace(mode, B, total_q), self.num_qo_heads, self.num_kv_heads,
+                             self._ensure_workspace(B, total_q), self.num_qo_heads, self.num_kv_heads,
                              self.head_dim)
         return AttentionMetadata(forward_mode=batch.forward_mode, kv_cache=self.kv_cache,
                                  output_kv_indices=out_slots, wrapper=plan)
@@ -397,9 +391,9 @@ class AttentionBackend:
         self._graph_scratch = torch.zeros(max_bs + 1, dtype=torch.int32, device=dev)
         self.slot_table.reserve(2 * max_bs, context_len)
         # one workspace, sized for the largest captured batch, shared by all graphs
-        self._graph_workspace = ops.decode_workspace_init(torch.empty(
+        self._graph_workspace = torch.empty(
             ops.decode_workspace_bytes(max_bs, self.num_qo_heads, self.num_kv_heads, self.head_dim),
-            dtype=torch.uint8, device=dev))
+            dtype=torch.uint8, device=dev)
         self._graph_context_len = context_len
 
     def build_metadata_for_cuda_graph_capture(self, graph, bs: int, context_len: int) -> AttentionMetadata:

@@ -113,17 +113,6 @@ def decode_workspace_bytes(B: int, Hq: int, Hkv: int, D: int) -> int:
     return int(_lib.load().b200_decode_workspace_bytes(B, Hq, Hkv, D))
 
 
-def decode_workspace_init(workspace: torch.Tensor) -> torch.Tensor:
-    """b200_decode_workspace_init: once per freshly allocated decode workspace, before its first decode.  The buffer
-    then belongs to decode: its first bytes hold state (arrival counters of the in-kernel merge) between calls."""
-    _need_cuda(workspace)
-    assert workspace.dtype == torch.uint8
-    _lib.check(_lib.load().b200_decode_workspace_init(workspace.data_ptr(), workspace.numel(), _stream()),
-               "b200_decode_workspace_init")
-    workspace._b200_ready = True
-    return workspace
-
-
 @torch.library.custom_op("b200attn::decode", mutates_args=("workspace",), device_types="cuda")
 def decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, kv_indptr: torch.Tensor,
            kv_indices: torch.Tensor, last_page_len: torch.Tensor, workspace: torch.Tensor, page_size: int,
@@ -140,10 +129,6 @@ def decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, kv_ind
     if B == 0:
         return out
     lib = _lib.load()
-    if not getattr(workspace, "_b200_ready", False):
-        # include/b200attn.h: the state at the start of a decode workspace is initialised once per buffer (tensor
-        # object); AttentionBackend does it when it allocates, this covers callers that bring their own buffer
-        decode_workspace_init(workspace)
     rc = lib.b200_decode(q.data_ptr(), q.stride(0), k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(-3),
                          kv_indptr.data_ptr(), kv_indices.data_ptr(), last_page_len.data_ptr(), out.data_ptr(),
                          out.stride(0), workspace.data_ptr(), workspace.numel(), B, Hq, Hkv, D, page_size,

@@ -53,23 +53,6 @@ def test_decode_vs_oracle(pkg, kv_lens, Hq, Hkv, ps):
     check_close(out, ref, f"decode {kv_lens[:4]} Hq{Hq} Hkv{Hkv} ps{ps}")
 
 
-def test_decode_workspace_state_survives_changing_batches(pkg):
-    """The decode workspace carries arrival counters between calls (in-kernel merge): a buffer sized for the largest
-    batch is reused for batches of different sizes and head counts' worth of tickets; every call must leave it clean."""
-    Hq, Hkv = 16, 8
-    cases = [make_paged_case(lens, Hq, Hkv, seed=i) for i, lens in
-             enumerate([[900, 2500, 17, 4000], [3000] * 40, [5, 0, 9], [20000], [700] * 9, [3000] * 40])]
-    ws = _ws(pkg, 40, Hq, Hkv, 128)
-    for rnd in range(2):
-        for case in cases:
-            d = dev(case)
-            out = pkg.ops.decode(d["q"], d["k_cache"], d["v_cache"], d["kv_indptr"], d["kv_indices"], d["last_page_len"],
-                                 ws, 1, 128 ** -0.5)
-            ref = orc.decode_attention(case["q"], case["k_cache"], case["v_cache"], case["kv_indptr"], case["kv_indices"],
-                                       case["last_page_len"], 1, return_fp32=True)
-            check_close(out, ref, f"round {rnd} lens {case['B']}")
-
-
 def test_decode_large_magnitude_and_repeat(pkg):
     """Scores with a wide dynamic range (softmax stability) and run-to-run determinism."""
     case = make_paged_case([900, 2500, 17], 32, 8, seed=11, scale=3.0)
@@ -337,8 +320,8 @@ def test_decode_properties_long_context(pkg):
 @pytest.mark.parametrize("ps", [16, 1])
 def test_decode_long_ragged_one_kv_head(pkg, ps):
     """Ranks with ONE KV head (TP8 shapes: every warp is its own stream) and ~1.4 M tokens of ragged context: every
-    output row against a direct fp32 computation on the device; three decode calls through the same (stateful)
-    workspace must agree."""
+    output row against a direct fp32 computation on the device; the same workspace serves a prefill call in between
+    and three decode calls, which must agree."""
     torch.manual_seed(1)
     rng = np.random.default_rng(3)
     B, Hq, Hkv, D = 48, 4, 1, 128
@@ -353,17 +336,16 @@ def test_decode_long_ragged_one_kv_head(pkg, ps):
     indptr_np = np.concatenate([[0], np.cumsum(pages)]).astype(np.int32)
     indptr = torch.from_numpy(indptr_np).cuda()
     last = torch.from_numpy((lens - (pages - 1) * ps).astype(np.int32)).cuda()
-    ws = _ws(pkg, B, Hq, Hkv, D)          # ONE decode workspace for all three calls: its arrival counters must come
-    wsp = _ws(pkg, 2, Hq, Hkv, D, 4096)   # back to zero after every call (in-kernel merge); prefill has its own buffer
+    ws = _ws(pkg, B, Hq, Hkv, D, total_q=4096)
     sm = D ** -0.5
     outs = []
     for rep in range(3):
         outs.append(pkg.ops.decode(q, k_cache, v_cache, indptr, perm, last, ws, ps, sm).float())
-        if rep == 0:    # a prefill call in between
+        if rep == 0:    # a prefill through the SAME workspace in between
             case = make_paged_case([300, 77], Hq, Hkv, q_lens=[300, 77], seed=4)
             d = dev(case)
             pkg.ops.prefill(d["q"], d["k_cache"], d["v_cache"], d["qo_indptr"], d["kv_indptr"], d["kv_indices"],
-                            d["last_page_len"], wsp, 1, sm, True)
+                            d["last_page_len"], ws, 1, sm, True)
     torch.cuda.synchronize()
     assert (outs[0] - outs[1]).abs().max() <= 1e-2 and (outs[0] - outs[2]).abs().max() <= 1e-2
     worst = 0.0
