@@ -121,6 +121,8 @@ class SlotTable:
         self._evt: list = [None] * self.RING
         self.last_msg_bytes = 0
         self.full_resends = 0           # sequences uploaded from position 0 (statistics / tests)
+        self.fast_decode = True         # direct packing of steady-state decode steps (tests switch it off to compare)
+        self._iota = None
 
     # -- capacity ----------------------------------------------------------------------------------
     def _grow(self, rows: int, cols: int) -> None:
@@ -243,6 +245,28 @@ class SlotTable:
             r = np.where(known, rows, 0)
             t = self.tracked[r]
             trusted &= (t == cach) & (t > 0) & (kvl >= t) & (kv_first == self.first[r]) & (kv_prev == self.last[r])
+        if self.fast_decode and B and not self.verify and bool(trusted.all()) and bool((kvl == cach + 1).all()):
+            # Steady-state decode (every sequence known and trusted, exactly one new slot each): the message and the
+            # bookkeeping of the general path below, written out directly (a dozen numpy calls instead of ~40; at the
+            # TP8 shapes the device step is 0.18 ms and this packing is most of the host's share of a step).
+            if page_size > 1:
+                head = cach % page_size == 0
+                if not bool(np.all(np.where(head, kv_last % page_size == 0, kv_last == self.last[rows] + 1))):
+                    self._check_pages(seqs, kv_last.astype(np.int32), cach, np.ones(B, np.int64), np.arange(B), page_size)
+            max_len = int(kvl.max())
+            if max_len > self.table.shape[1]:
+                self._grow(self.table.shape[0], max(max_len, 2 * self.table.shape[1]))
+            if self._iota is None or self._iota.size < B:
+                self._iota = np.arange(max(B, 256), dtype=np.int64)
+            qls = ntok - cach
+            msg = np.empty(8 * B, dtype=np.int32)
+            m = msg.reshape(8, B)
+            m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7] = rows, kvl, cach, qls, cach, 1, self._iota[:B], kv_last
+            self.last[rows] = kv_last
+            self.tracked[rows] = kvl
+            dev = self._upload(msg)
+            self.last_msg_bytes = msg.nbytes
+            return dev, B, int(qls.sum()), int(kvl.sum()), B
         n_unknown = int(B - known.sum())
         if n_unknown:
             self._take_rows(n_unknown)

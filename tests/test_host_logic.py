@@ -203,3 +203,25 @@ def test_pack_step_degenerate_sequences_and_page_run_check(pkg):
         s_.cached_kv_len = len(s_.kv_indices); s_.token_ids.append(0); s_.kv_indices.append(nxt)
     with pytest.raises(ValueError, match="page-aligned"):
         st4.pack_step(seqs, 4)
+
+
+def test_steady_state_decode_fast_path_equals_general_path(pkg):
+    """Steady-state decode steps are packed by a direct path; message, counters and fingerprints must equal the
+    general path's, step after step, at page size 1 and 4, and a step that is not steady (a new sequence joins)
+    must take the general path on both."""
+    for ps in (1, 4):
+        tabs = [pkg.SlotTable(torch.device("cpu"), rows=4, cols=16) for _ in range(2)]
+        tabs[1].fast_decode = False
+        base = [100, 200, 300]
+        seqs = [S(f"s{i}", 5 + i, range(b, b + 5 + i), 0) for i, b in enumerate(base)]
+        for step in range(12):
+            if step == 6:                  # a fourth sequence is admitted: not a steady step
+                seqs.append(S("late", 3, range(400, 403), 0))
+            outs = [t.pack_step(seqs, ps) for t in tabs]
+            assert np.array_equal(outs[0][0].numpy(), outs[1][0].numpy()), (ps, step)
+            assert outs[0][1:] == outs[1][1:], (ps, step, outs[0][1:], outs[1][1:])
+            for name in ("tracked", "first", "last"):
+                assert np.array_equal(getattr(tabs[0], name), getattr(tabs[1], name)), (ps, step, name)
+            assert tabs[0].full_resends == tabs[1].full_resends
+            for q in seqs:
+                q.cached_kv_len = len(q.kv_indices); q.token_ids.append(0); q.kv_indices.append(q.kv_indices[-1] + 1)
