@@ -3,10 +3,11 @@
  *
  * One shared library (libb200attn.so, nvcc -gencode arch=compute_100a,code=sm_100a).  Plain
  * pointers and sizes only; every pointer is a DEVICE pointer owned by the caller (PyTorch in
- * the shipped host side) unless the name ends in `_host`.  The library owns no device memory,
- * never allocates, never synchronises and launches only on the stream it is given, so every
- * entry point can be captured in a CUDA graph (reference: core/cuda_graph.py:27-39,
- * core/model_runner.py:407-416).
+ * the shipped host side) unless the name ends in `_host`.  The library owns no device memory
+ * (one exception: the fixed scratch array of b200_decode_noalloc, section 3b),
+ * never allocates, never synchronises and launches only on the stream it is given, so the
+ * entry points that take all their memory from the caller can be captured in a CUDA graph
+ * (reference: core/cuda_graph.py:27-39, core/model_runner.py:407-416).
  *
  * Return value: 0 on success, non-zero on error; b200_last_error() then returns a
  * thread-local message.  Asynchronous faults surface on the caller's next sync, as with the
@@ -126,6 +127,35 @@ int b200_decode(const void* q, int64_t q_row_stride, const void* k_cache, const 
                 const int32_t* last_page_len, void* out, int64_t out_row_stride, void* workspace,
                 size_t workspace_bytes, int32_t B, int32_t Hq, int32_t Hkv, int32_t D,
                 int32_t page_size, float sm_scale, int32_t dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (3b) b200_decode without a workspace argument.  NO COUNTERPART IN THE REFERENCE: FlashInfer's
+ *     wrappers are given a torch workspace tensor (layers/attention.py:44-48) and every host of the
+ *     reference has torch's allocator.  This entry point is for hosts of the C ABI that cannot obtain
+ *     device memory when they call: the engine gave all free HBM to the KV pool at start-up
+ *     (core/model_runner.py:113-144 sizes the pool that way), cudaMalloc / cudaFree are off limits
+ *     because they stall every stream of a running worker, or the caller is a foreign-language
+ *     binding / plugin thread with no device allocator at hand.
+ *
+ *     Same arguments, kernels and results as b200_decode; the split-KV partials go to an array of
+ *     B200_DECODE_NOALLOC_SCRATCH_BYTES that is part of the library image.  Consequences:
+ *       - every GPU on which the library's module is loaded gives up that many bytes until exit;
+ *       - shapes with b200_decode_workspace_bytes(B, Hq, Hkv, D) above the limit are refused
+ *         (non-zero return, message with both sizes) -- use b200_decode for those;
+ *       - the array is shared by all calls on a device and is not cleared between them (the kernels
+ *         write every word they later read, so stale contents are harmless); calls issued on one
+ *         stream are ordered, calls that may run at the same time on the GPU race on it;
+ *       - the first call on each device resolves the array's device address (cudaGetSymbolAddress,
+ *         which may load the module): make that call with the device current and outside any stream
+ *         capture.  The call allocates nothing and frees nothing, then or later.
+ * ---------------------------------------------------------------------------------------- */
+#define B200_DECODE_NOALLOC_SCRATCH_BYTES (8u << 20)
+
+int b200_decode_noalloc(const void* q, int64_t q_row_stride, const void* k_cache, const void* v_cache,
+                        int64_t kv_slot_stride, const int32_t* kv_indptr, const int32_t* kv_indices,
+                        const int32_t* last_page_len, void* out, int64_t out_row_stride, int32_t B,
+                        int32_t Hq, int32_t Hkv, int32_t D, int32_t page_size, float sm_scale,
+                        int32_t dtype, b200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * (4) Ragged paged prefill attention (prefix pages + new tokens, bottom-right causal).

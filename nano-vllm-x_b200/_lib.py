@@ -29,6 +29,8 @@ SIGNATURES = {
     "b200_decode_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32]),
     "b200_decode": (_i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i32, _i32,
                            _i32, _i32, _i32, _f32, _i32, _vp]),
+    "b200_decode_noalloc": (_i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32,
+                                   _i32, _f32, _i32, _vp]),
     "b200_prefill_workspace_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),
     "b200_prefill": (_i32, [_vp, _i64, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i32,
                             _i32, _i32, _i32, _i32, _i32, _f32, _i32, _i32, _vp]),
