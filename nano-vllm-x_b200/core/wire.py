@@ -116,9 +116,13 @@ class BatchEncoder:
 class BatchDecoder:
     """Worker side: applies a message to the mirror sequences and returns the step's ForwardBatch."""
 
-    def __init__(self, sequence_cls=Sequence, batch_cls=ForwardBatch, mode_cls=ForwardMode):
+    def __init__(self, sequence_cls=Sequence, batch_cls=ForwardBatch, mode_cls=ForwardMode, on_drop=None):
+        """``on_drop(seq_id)`` is called whenever the worker must stop trusting what it holds for a sequence: its
+        handle was dropped by the scheduler (finish / preempt) or the scheduler resent it in full.  The binding uses
+        it to call ``SlotTable.forget`` so that a reused seq_id can never meet a stale device row."""
         self._seqs: dict[int, object] = {}
         self._sequence_cls, self._batch_cls, self._mode_cls = sequence_cls, batch_cls, mode_cls
+        self._on_drop = on_drop
 
     def decode(self, data) -> ForwardBatch:
         m = np.frombuffer(data, dtype="<i4")
@@ -127,7 +131,9 @@ class BatchDecoder:
         mode = self._mode_cls.PREFILL if int(m[1]) == 0 else self._mode_cls.DECODE
         B, n_drop, verify = int(m[2]), int(m[3]), bool(m[4] & 1)
         for h in m[5:5 + n_drop].tolist():
-            self._seqs.pop(h, None)
+            gone = self._seqs.pop(h, None)
+            if gone is not None and self._on_drop is not None:
+                self._on_drop(gone.seq_id)
         pos = 5 + n_drop
         w = m.tolist()                     # one conversion; the loop below touches plain ints only
         rec_end = pos + _REC * B
@@ -140,6 +146,8 @@ class BatchDecoder:
             if kind == 1:
                 seq_id, sp = pickle.loads(m[pos:pos + blob_words].tobytes())
                 pos += blob_words
+                if self._on_drop is not None:
+                    self._on_drop(seq_id)        # a full record restarts the sequence: drop whatever row it had
                 s = self._sequence_cls(seq_id=seq_id)
                 if sp is not None:
                     s.sampling_params = sp

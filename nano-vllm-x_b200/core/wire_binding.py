@@ -11,7 +11,9 @@ that transport (same queues, same request envelope, same method name) and change
   (core/scheduler.py:140-153, 173-190), so a re-admitted sequence is resent in full;
 * worker process: ``Worker.execute_model`` accepts bytes, applies them to its ``BatchDecoder`` (mirror
   ``Sequence`` objects of the reference's own class) and runs the unchanged model runner on the rebuilt
-  ``ForwardBatch``.  A lost or corrupted message raises in the worker instead of desynchronising it.
+  ``ForwardBatch``.  A lost or corrupted message raises in the worker instead of desynchronising it.  Handles the
+  scheduler drops (finish / preempt) and sequences it resends in full also make the worker's attention backend
+  forget its device slot row (``SlotTable.forget``): the finish signal the pickle transport does not have.
 """
 from __future__ import annotations
 
@@ -58,7 +60,14 @@ def install(verify: bool = False) -> None:
         if isinstance(batch, (bytes, bytearray, memoryview)):
             dec = getattr(self, "_b200_decoder", None)
             if dec is None:
-                dec = self._b200_decoder = BatchDecoder(sequence_cls=Sequence, batch_cls=ForwardBatch, mode_cls=ForwardMode)
+                def on_drop(seq_id, worker=self):
+                    # finish / preempt / full resend: the attention backend's device row of that id is stale from now
+                    # on (the stock FlashInfer backend keeps no rows and has no slot_table)
+                    table = getattr(getattr(getattr(worker, "model_runner", None), "attn_backend", None), "slot_table", None)
+                    if table is not None:
+                        table.forget(seq_id)
+                dec = self._b200_decoder = BatchDecoder(sequence_cls=Sequence, batch_cls=ForwardBatch, mode_cls=ForwardMode,
+                                                        on_drop=on_drop)
             batch = dec.decode(batch)
         return orig_worker_execute(self, batch)
 

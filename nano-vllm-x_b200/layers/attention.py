@@ -97,6 +97,14 @@ class SlotTable:
     from the ones this row holds (``cached_kv_len = P`` with new prefix slots); a
     ``seq_id`` reused after its first owner finished (request ids are caller-supplied,
     entrypoints/openai/serving_completion.py:39).  ``forget(seq_id)`` drops a row explicitly.
+
+    The three-slot fingerprint cannot see slots that changed in the MIDDLE of a row (finish-time prefix
+    caching replaces ``kv[old_prefix:new_prefix]`` by the tree's copies, core/kv_cache.py:333-369; a later
+    request with the same id can then come back with the same length, first slot and last slot).  The
+    reference only re-maps slots between a sequence's runs, and every run starts with a PREFILL batch
+    (core/scheduler.py:67-80 admits from ``waiting`` only), so PREFILL steps additionally compare a
+    position-weighted checksum of ``kv[:tracked]`` with the one accumulated while the row was uploaded
+    (O(L) per trusted sequence, on the step that is O(L^2) on the device anyway); DECODE steps keep the O(1) check.
     ``B200ATTN_VERIFY=1`` additionally keeps a full host mirror and checks every step (debug aid;
     O(sum L) like the reference).
     """
@@ -110,6 +118,7 @@ class SlotTable:
         self.tracked = np.zeros(rows, dtype=np.int64)
         self.first = np.full(rows, -1, dtype=np.int64)
         self.last = np.full(rows, -1, dtype=np.int64)
+        self.csum = np.zeros(rows, dtype=np.int64)      # sum(slot[p] * (p % 65521 + 1)) over the tracked prefix, mod 2^64
         self.last_used = np.zeros(rows, dtype=np.int64)
         self.owner: list = [None] * rows
         self.free_rows = list(range(rows - 1, -1, -1))
@@ -140,6 +149,7 @@ class SlotTable:
             self.tracked = np.concatenate([self.tracked, np.zeros(extra, np.int64)])
             self.first = np.concatenate([self.first, np.full(extra, -1, np.int64)])
             self.last = np.concatenate([self.last, np.full(extra, -1, np.int64)])
+            self.csum = np.concatenate([self.csum, np.zeros(extra, np.int64)])
             self.last_used = np.concatenate([self.last_used, np.zeros(extra, np.int64)])
             self.owner += [None] * extra
 
@@ -155,6 +165,7 @@ class SlotTable:
             self.owner[row] = None
             self.tracked[row] = 0
             self.first[row] = self.last[row] = -1
+            self.csum[row] = 0
             self.free_rows.append(row)
 
     def _take_rows(self, need: int) -> None:
@@ -206,9 +217,21 @@ class SlotTable:
                     f"page-aligned runs of {ps} consecutive slots; the reference's token-granular KVCacheAllocator "
                     "(core/kv_cache.py:101-117) needs page_size=1")
 
+    @staticmethod
+    def _weighted_sum(slots, start: int) -> int:
+        """sum(slots[j] * ((start + j) % 65521 + 1)) as a wrapped int64 (the row checksum's increment)."""
+        a = np.asarray(slots, dtype=np.int64)
+        if a.size == 0:
+            return 0
+        with np.errstate(over="ignore"):
+            return int((a * ((np.arange(start, start + a.size, dtype=np.int64) % 65521) + 1)).sum())
+
     # -- per step ----------------------------------------------------------------------------------
-    def pack_step(self, seqs, page_size: int = 1) -> tuple[torch.Tensor, int, int, int, int]:
+    def pack_step(self, seqs, page_size: int = 1, prefill: bool = False) -> tuple[torch.Tensor, int, int, int, int]:
         """Returns (device message, n_payload, total_q, total_kv, total_new).
+
+        ``prefill=True`` (a PREFILL batch: the only place a sequence can come back with re-mapped slots) makes every
+        trusted row prove itself with the O(L) checksum described in the class docstring; a mismatch is a full resend.
 
         ``page_size > 1`` (an extension: the reference is token granular, layers/attention.py:66) needs every
         page of a sequence to be ``page_size`` consecutive, page-aligned slots; the newly uploaded slots are
@@ -245,6 +268,12 @@ class SlotTable:
             r = np.where(known, rows, 0)
             t = self.tracked[r]
             trusted &= (t == cach) & (t > 0) & (kvl >= t) & (kv_first == self.first[r]) & (kv_prev == self.last[r])
+            if prefill:
+                for i in np.flatnonzero(trusted):
+                    n = int(self.tracked[rows[i]])
+                    kv = seqs[i].kv_indices
+                    if np.int64(self._weighted_sum(kv if n == len(kv) else kv[:n], 0)) != self.csum[rows[i]]:
+                        trusted[i] = False          # same ends, different middle: resend the row
         if self.fast_decode and B and not self.verify and bool(trusted.all()) and bool((kvl == cach + 1).all()):
             # Steady-state decode (every sequence known and trusted, exactly one new slot each): the message and the
             # bookkeeping of the general path below, written out directly (a dozen numpy calls instead of ~40; at the
@@ -264,6 +293,7 @@ class SlotTable:
             m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7] = rows, kvl, cach, qls, cach, 1, self._iota[:B], kv_last
             self.last[rows] = kv_last
             self.tracked[rows] = kvl
+            self.csum[rows] += kv_last * (cach % 65521 + 1)         # the new slot sits at position cach (wraps like _weighted_sum)
             dev = self._upload(msg)
             self.last_msg_bytes = msg.nbytes
             return dev, B, int(qls.sum()), int(kvl.sum()), B
@@ -286,13 +316,19 @@ class SlotTable:
             np.cumsum(cnt[:-1], out=woff[1:])
         n_payload = int(cnt.sum())
         payload = np.empty(n_payload, dtype=np.int32)
+        # row checksums: a row (re)sent from position 0 starts over, a delta adds to what the row has
         if n_payload == B and bool((cnt == 1).all()):            # steady-state decode: one new slot per sequence
             payload[:] = kv_last
+            self.csum[rows] = np.where(start == 0, 0, self.csum[rows]) + kv_last * (start % 65521 + 1)
         else:
+            self.csum[rows[start == 0]] = 0
             for i in np.flatnonzero(cnt):
                 a, c = int(woff[i]), int(cnt[i])
                 kv = seqs[i].kv_indices
                 payload[a:a + c] = kv if c == len(kv) else kv[len(kv) - c:]
+                base = self.csum[rows[i]] if start[i] else np.int64(0)
+                with np.errstate(over="ignore"):
+                    self.csum[rows[i]] = base + np.int64(self._weighted_sum(payload[a:a + c], int(start[i])))
         self.full_resends += int(((start == 0) & (kvl > 0)).sum())
         if page_size > 1 and n_payload:
             if n_payload == B and bool(trusted.all()) and bool((cnt == 1).all()):
@@ -375,7 +411,7 @@ class AttentionBackend:
         mode = mode_name(batch.forward_mode)
         st = self.slot_table
         ps = self.page_size
-        msg, n_payload, total_q, total_kv, total_new = st.pack_step(seqs, ps)
+        msg, n_payload, total_q, total_kv, total_new = st.pack_step(seqs, ps, prefill=(mode == "PREFILL"))
         if ps == 1:
             n_pages = total_kv
         else:

@@ -135,6 +135,43 @@ def test_seq_id_reused_after_finish_and_forget(pkg):
     st.forget("never-seen")
 
 
+def test_seq_id_reused_with_slots_remapped_in_the_middle_of_the_row(pkg, monkeypatch):
+    """finish-time prefix caching replaces kv[old_prefix:new_prefix] by the tree's copies
+    (core/kv_cache.py:333-369) and frees the private duplicates; a later request that reuses the seq_id can be
+    admitted with cached_kv_len == the old tracked length, the SAME first slot and the SAME kv[P-1].  Nobody told the
+    worker that the first owner finished (the pickle transport has no finish signal), so the O(1) fingerprint passes.
+    Every run of a sequence starts with a PREFILL batch (core/scheduler.py:67-80); there the row checksum must notice
+    the re-mapped middle and resend the row instead of attending freed slots."""
+    monkeypatch.delenv("B200ATTN_VERIFY", raising=False)
+    st = pkg.SlotTable(torch.device("cpu"), rows=4, cols=64)
+    a = S("req-7", 12, range(100, 112), 0)
+    assert st.pack_step([a], prefill=True)[1] == 12
+    for _ in range(4):                                   # decode steps through the fast path keep the checksum current
+        a.cached_kv_len = len(a.kv_indices); a.token_ids.append(0); a.kv_indices.append(200 + len(a.kv_indices))
+        assert st.pack_step([a])[1] == 1
+    tracked = len(a.kv_indices)                          # 16
+    assert int(st.csum[st.row_of["req-7"]]) == st._weighted_sum(a.kv_indices, 0)
+    # same id, same length, same first and last cached slot, positions 4..11 now served from the tree's slots
+    kv2 = list(a.kv_indices)
+    kv2[4:12] = range(900, 908)
+    b = S("req-7", tracked + 3, kv2 + [300, 301, 302], tracked)
+    assert b.kv_indices[0] == a.kv_indices[0] and b.kv_indices[tracked - 1] == a.kv_indices[tracked - 1]
+    before = st.full_resends
+    msg, n_payload, *_ = st.pack_step([b], prefill=True)
+    assert n_payload == len(b.kv_indices) and st.full_resends == before + 1
+    table = np.zeros((4, 64), np.int32)
+    apply_update(table, msg.numpy(), 1, n_payload)
+    assert table[st.row_of["req-7"], :len(b.kv_indices)].tolist() == b.kv_indices
+    assert int(st.csum[st.row_of["req-7"]]) == st._weighted_sum(b.kv_indices, 0)
+    # an honest chunked-prefill continuation (nothing moved) is still a delta on a PREFILL step
+    b.cached_kv_len = len(b.kv_indices); b.token_ids += [0, 0]; b.kv_indices += [303, 304]
+    assert st.pack_step([b], prefill=True)[1] == 2 and st.full_resends == before + 1
+    # a swap of two interior slots keeps every plain sum; the position weights catch it
+    c = S("req-7", len(b.kv_indices) + 1, list(b.kv_indices) + [305], len(b.kv_indices))
+    c.kv_indices[5], c.kv_indices[6] = c.kv_indices[6], c.kv_indices[5]
+    assert st.pack_step([c], prefill=True)[1] == len(c.kv_indices)
+
+
 def test_rows_of_the_current_batch_are_never_evicted(pkg):
     """Two rows, both owned by sequences of this step, plus newcomers: the table must grow, not recycle rows of
     sequences that the packing loop has not reached yet."""
@@ -220,7 +257,7 @@ def test_steady_state_decode_fast_path_equals_general_path(pkg):
             outs = [t.pack_step(seqs, ps) for t in tabs]
             assert np.array_equal(outs[0][0].numpy(), outs[1][0].numpy()), (ps, step)
             assert outs[0][1:] == outs[1][1:], (ps, step, outs[0][1:], outs[1][1:])
-            for name in ("tracked", "first", "last"):
+            for name in ("tracked", "first", "last", "csum"):
                 assert np.array_equal(getattr(tabs[0], name), getattr(tabs[1], name)), (ps, step, name)
             assert tabs[0].full_resends == tabs[1].full_resends
             for q in seqs:

@@ -114,3 +114,39 @@ def test_decoder_rejects_lost_or_corrupt_messages(pkg):
     b.kv_indices[1] = 99; b.token_ids.append(4); b.kv_indices.append(10); b.cached_kv_len = 3
     with pytest.raises(ValueError):
         dec2.decode(enc2.encode(pkg.ForwardBatch(pkg.ForwardMode.DECODE, 1, [b])))
+
+
+def test_dropped_and_resent_sequences_make_the_worker_forget_its_slot_row(pkg):
+    """the worker's SlotTable never heard that a sequence finished.  With the delta wire it does:
+    the decoder reports every dropped handle and every full resend, and the binding (core/wire_binding.py) forwards
+    that to SlotTable.forget, so a reused seq_id whose middle slots were re-mapped meets no stale row."""
+    import torch
+    from importlib import import_module
+    wire = import_module("nano-vllm-x_b200.core.wire")
+    table = pkg.SlotTable(torch.device("cpu"), rows=4, cols=64)
+    dropped = []
+
+    def on_drop(seq_id):
+        dropped.append(seq_id)
+        table.forget(seq_id)
+
+    enc, dec = wire.BatchEncoder(), wire.BatchDecoder(on_drop=on_drop)
+    a = pkg.Sequence("req-1", list(range(12)), list(range(100, 112)), 0)
+    got = dec.decode(enc.encode(pkg.ForwardBatch(pkg.ForwardMode.PREFILL, 1, [a])))
+    assert dropped == ["req-1"]                          # first sight is a full record: nothing to forget yet, harmless
+    assert table.pack_step(got.seqs, prefill=True)[1] == 12
+    a.cached_kv_len = 12; a.token_ids.append(0); a.kv_indices.append(300)
+    got = dec.decode(enc.encode(pkg.ForwardBatch(pkg.ForwardMode.DECODE, 1, [a])))
+    assert dropped == ["req-1"] and table.pack_step(got.seqs)[1] == 1        # a delta step reports nothing
+    # the scheduler finishes it (wire_binding's finish_sequence hook), then the id comes back with the same length,
+    # the same first / last cached slot and tree-owned slots in the middle
+    enc.forget("req-1")
+    kv = list(a.kv_indices)
+    kv[3:9] = range(900, 906)
+    b = pkg.Sequence("req-1", list(range(14)), kv + [301], 13)
+    before = table.full_resends
+    got = dec.decode(enc.encode(pkg.ForwardBatch(pkg.ForwardMode.PREFILL, 1, [b])))
+    assert dropped == ["req-1", "req-1", "req-1"]        # the dropped handle, then the full record
+    assert "req-1" not in table.row_of
+    # the row is gone, so even the O(1) path (prefill=False) has to upload everything
+    assert table.pack_step(got.seqs)[1] == 14 and table.full_resends == before + 1
