@@ -13,12 +13,19 @@ as wrappers around the reference's own classes — nothing in the reference tree
    as ``kv_indices[:P]`` with ``cached_kv_len = P``, pins the matched path (``inc_ref``) and records
    ``(P, node)`` in ``KVCacheManager.unfinished_sequences`` — the bookkeeping ``cache_sequence`` already reads.
 2. ``Scheduler.free_kv_slots`` (core/scheduler.py:130-138, preemption): the first ``P`` slots belong to the tree,
-   only the private tail is freed and the pin is dropped.
+   only the private tail is freed and the pin is dropped.  (Reached through ``Scheduler.preempt`` for a sequence
+   that is still in ``running``.  The stock memory-pressure path, core/scheduler.py:98-101, pops the victim from
+   ``running`` BEFORE calling ``preempt``, which then returns at its ``if not seq in self.running`` guard (:146-147):
+   in the shipped engine that preemption is a no-op and the victim simply leaves the queue.  That is reference
+   behaviour outside this row and is left as it is.)  If the pool cannot supply the private tail at admission,
+   the adoption of step 1 is undone before the error propagates.
 3. ``KVCacheManager.cache_sequence`` (core/kv_cache.py:333-369), three fixes the hook exposes:
    * tokens without KV are not inserted: at finish ``token_ids`` is one longer than ``kv_indices``
      (core/scheduler.py:161-171 appends the sampled token), and ``RadixTree.insert`` slices key and value by the
      same prefix length (:193-194), so the stock call stores nodes whose value is shorter than their key and a
-     later match would return slots shifted against token positions;
+     later match would return slots shifted against token positions; slots allocated but not yet computed
+     (``kv_indices`` beyond ``cached_kv_len``: a sequence finished between scheduling and its update) go back
+     to the allocator instead of into the tree;
    * the duplicate-slot leak: slots in ``[old_prefix_len, new_prefix_len)`` duplicate slots the tree already
      holds and are freed only ``if old_prefix_len != 0`` (:353-357); a sequence first cached at finish
      (``old_prefix_len == 0``, every sequence of the stock engine) leaks them;
@@ -59,10 +66,16 @@ def install() -> None:
     def cache_sequence(self, seq):
         """core/kv_cache.py:333-369 with the three fixes listed in the module docstring."""
         tree = self.radix_tree
-        n = len(seq.kv_indices)
-        key = seq.token_ids[:n]                         # only tokens that HAVE a KV row
+        # only tokens whose KV row has been COMPUTED: a sequence finished or aborted between schedule() and
+        # update_sequence() (abort while a pipeline-parallel step is in flight, core/engine.py step_with_pp) owns
+        # slots beyond cached_kv_len that were never written; they must not become valid KV in the tree
+        n = min(len(seq.kv_indices), seq.cached_kv_len)
+        if seq.status == SequenceStatus.FINISHED and n < len(seq.kv_indices):
+            self.kv_cache_allocator.free(seq.kv_indices[n:])
+            del seq.kv_indices[n:]
+        key = seq.token_ids[:n]
         old_prefix_len, old_last_node = self.unfinished_sequences.get(seq.seq_id, (0, tree.root))
-        new_prefix_len, new_last_node = tree.insert(key, seq.kv_indices)
+        new_prefix_len, new_last_node = tree.insert(key, seq.kv_indices[:n])
         new_indices, _ = tree.match_prefix(key)
         if new_prefix_len > old_prefix_len:             # our copies of rows the tree already holds: free ours, adopt the tree's
             self.kv_cache_allocator.free(seq.kv_indices[old_prefix_len:new_prefix_len])
@@ -88,6 +101,17 @@ def install() -> None:
                 seq.cached_kv_len = len(indices)
                 km.radix_tree.inc_ref(node)
                 km.unfinished_sequences[seq.seq_id] = (len(indices), node)
+                try:
+                    orig_alloc(self, seq)
+                except Exception:
+                    # pool full at admission (core/scheduler.py:71 has no try): give the prefix back, or the pinned
+                    # path could never be evicted again and a retry would find the sequence half admitted
+                    km.radix_tree.dec_ref(node)
+                    km.unfinished_sequences.pop(seq.seq_id, None)
+                    seq.kv_indices.clear()
+                    seq.cached_kv_len = 0
+                    raise
+                return
         orig_alloc(self, seq)
 
     def free_kv_slots(self, seq):

@@ -155,3 +155,50 @@ def test_preemption_with_a_pinned_prefix_and_random_workload_conserve_slots(ref)
         _run_step(sched, C, lambda s: 3)
     _check_conservation(sched, size)
     assert n > 50
+
+
+def test_failed_admission_gives_the_adopted_prefix_back(ref):
+    """alloc_kv_slots adopts and pins the matched prefix before the stock allocation; when the pool
+    cannot supply the private tail the RuntimeError must leave nothing behind (no pin, no half-admitted sequence)."""
+    S, C = ref
+    size = 48
+    sched = S.Scheduler(kv_cache_size=size, max_bs=8)
+    a = _seq(C, "a", range(100, 120), 2)
+    sched.add_sequence(a)
+    while sched.has_unfinished_sequences():
+        _run_step(sched, C, lambda s: 7)
+    km = sched.kv_manager
+    tree = km.radix_tree
+    _, node = tree.match_prefix(list(range(100, 120)))
+    ref_before = node.ref_count if hasattr(node, "ref_count") else None
+    big = _seq(C, "big", list(range(100, 120)) + list(range(1000, 1000 + size)), 1)   # shares 20 tokens, needs > pool
+    with pytest.raises(RuntimeError):
+        sched.alloc_kv_slots(big)
+    assert big.kv_indices == [] and big.cached_kv_len == 0
+    assert "big" not in km.unfinished_sequences
+    if ref_before is not None:
+        assert node.ref_count == ref_before
+    # (the failed attempt may have evicted unpinned leaves, core/kv_cache.py:322-326: the free list can only have grown)
+    _check_conservation(sched, size)
+    # the same request can be admitted once there is room: nothing was left half done
+    ok = _seq(C, "ok", list(range(100, 120)) + [1, 2, 3], 1)
+    sched.alloc_kv_slots(ok)
+    assert ok.cached_kv_len == 20 and len(ok.kv_indices) == 23
+
+
+def test_slots_scheduled_but_never_computed_do_not_enter_the_tree(ref):
+    """a sequence finished between schedule() and update_sequence() (abort with a step in flight) has
+    kv_indices longer than cached_kv_len.  Those rows were never written; cache_sequence must free them, not cache them."""
+    S, C = ref
+    size = 64
+    sched = S.Scheduler(kv_cache_size=size, max_bs=8)
+    a = _seq(C, "a", range(10, 30), 8)
+    sched.add_sequence(a)
+    _run_step(sched, C, lambda s: 5)                      # prefill computed: cached_kv_len 20, 21 tokens
+    batch = sched.schedule()                              # decode step scheduled: slot 21 allocated, not computed
+    assert batch.seqs == [a] and len(a.kv_indices) == 21 and a.cached_kv_len == 20
+    sched.finish_sequence(a)                              # aborted before the step's result came back
+    _check_conservation(sched, size)
+    idx, _ = sched.kv_manager.radix_tree.match_prefix(list(range(10, 30)) + [5, 5])
+    assert len(idx) == 20, "an uncomputed slot was cached as valid KV"
+    assert len(_tree_slots(sched.kv_manager.radix_tree)) == 20
