@@ -189,10 +189,12 @@ def run_reference_arm(args):
         return
     # one host runs the WHOLE job's heads (the GPU arm shards them over the ranks; total work is fixed)
     Hq, Hkv, D = 32, 8, 128
-    val, dt, threads, _ = cpu_port_gbps(min(args.cpu_sample_seqs, args.batch), args.ctx, Hq, Hkv, D, args.page_size,
+    n_sample = min(args.cpu_sample_seqs, args.batch)
+    val, dt, threads, _ = cpu_port_gbps(n_sample, args.ctx, Hq, Hkv, D, args.page_size,
                                         steps=max(args.steps, 1), warmup=args.warmup)
-    sample = (f"{args.cpu_sample_seqs} of {args.batch} sequences x {args.ctx} tokens per step" +
-              (" (the whole workload)" if args.cpu_sample_seqs >= args.batch else ", same shapes"))
+    sample = (f"{n_sample} of {args.batch} sequences x {args.ctx} tokens per step" +
+              (" (the whole workload)" if n_sample >= args.batch else
+               ", same shapes; ms_per_step is the time of this sample, not of the whole batch"))
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
@@ -657,14 +659,17 @@ def run_b200_arm(args):
     if rank == 0 and tp == 1 and not args.no_cpu_baseline:
         val, dt, threads, n_pass = cpu_port_gbps(min(args.cpu_sample_seqs, B), L, Hq, Hkv, D, ps, steps=None, warmup=1)
         cpu = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"{args.cpu_sample_seqs} of {B} sequences x {L} tokens" +
+               "sample": f"{min(args.cpu_sample_seqs, B)} of {B} sequences x {L} tokens" +
                          (" (the whole workload)" if args.cpu_sample_seqs >= B else " (same shapes)") +
                          f", {n_pass} passes of {dt:.2f} s"}
 
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "decode_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch") if tp == 1 else None   # captured at TP1 shapes
+            cap = json.load(f)
+        # a static ncu figure: only quoted when this run launches the kernel on exactly the captured shapes
+        if tp == 1 and cap.get("algorithmic_bytes_per_launch") == algorithmic_bytes(B, L, Hq, Hkv, D, ps):
+            traffic = cap.get("dram_bytes_per_launch")
     except Exception:
         pass
 
