@@ -58,6 +58,8 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-prefill", action="store_true", help="skip the prefill (tensor-pipe) extra key")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip the FlashInfer-on-the-same-inputs extra key")
+    ap.add_argument("--no-m3", action="store_true",
+                    help="skip the extra keys store_kv / meta / decode_page1 (BASELINE.md M3 and the page-size-1 headline)")
     ap.add_argument("--no-engine", action="store_true",
                     help="skip the engine extra key (stock reference engine, FlashInfer arm and b200 arm, bench.py workload)")
     ap.add_argument("--engine-model", default="8b", choices=["0.6b", "8b"])
@@ -257,12 +259,33 @@ def make_prefill_case(q_lens, Hq, Hkv, D, devc, seed):
                 last_page_len=last, T=T, B=len(q_lens), q_lens=list(q_lens))
 
 
+def make_shared_prefix_case(Hq, Hkv, D, devc, seed, B=256, P=2048):
+    """BASELINE.json configs[3] / SURVEY.md 8(d) config 4 at the kernel: B sequences whose first P KV slots are the SAME
+    P slots (one radix-tree path) + a private suffix of randint(16, 256) new tokens each; page size 1."""
+    rng = np.random.default_rng(seed)
+    suffix = rng.integers(16, 257, size=B)
+    T = int(suffix.sum())
+    n_slots = P + T + 64
+    perm = rng.permutation(n_slots).astype(np.int32)
+    qo = np.concatenate([[0], np.cumsum(suffix)]).astype(np.int32)
+    kvp = np.concatenate([[0], np.cumsum(P + suffix)]).astype(np.int32)
+    idx = np.concatenate([np.concatenate([perm[:P], perm[P + qo[i]:P + qo[i + 1]]]) for i in range(B)]).astype(np.int32)
+    g = torch.Generator(device=devc).manual_seed(seed)
+    rnd = lambda *shape: torch.randn(shape, device=devc, dtype=torch.bfloat16, generator=g)
+    return dict(q=rnd(T, Hq, D), k_cache=rnd(n_slots, Hkv, D), v_cache=rnd(n_slots, Hkv, D),
+                qo_indptr=torch.from_numpy(qo).to(devc), kv_indptr=torch.from_numpy(kvp).to(devc),
+                kv_indices=torch.from_numpy(idx).to(devc), last_page_len=torch.ones(B, dtype=torch.int32, device=devc),
+                T=T, B=B, q_lens=[int(x) for x in suffix], prefix_lens=[P] * B)
+
+
 def prefill_cases(Hq, Hkv, D, devc):
     from oracle.paged_attention_oracle import bench_workload      # request generator of the reference's bench.py:14-29
     plens = [len(p) for p in bench_workload()[0]]
     return [("bench_prompts_256 (one prefill step of the reference bench.py workload: 256 prompts, 142 827 tokens, page 1)",
              make_prefill_case(plens, Hq, Hkv, D, devc, 11)),
-            ("uniform_16x4096 (16 sequences x 4096 tokens, causal, page 1)", make_prefill_case([4096] * 16, Hq, Hkv, D, devc, 12))]
+            ("uniform_16x4096 (16 sequences x 4096 tokens, causal, page 1)", make_prefill_case([4096] * 16, Hq, Hkv, D, devc, 12)),
+            ("shared_prefix_256x2048 (config 4: 256 sequences, the SAME 2048 cached prefix slots + randint(16,256) new tokens "
+             "each, page 1)", make_shared_prefix_case(Hq, Hkv, D, devc, 13))]
 
 
 def bench_prefill(pkg, Hq, Hkv, D, devc, stream, iters=10):
@@ -276,13 +299,13 @@ def bench_prefill(pkg, Hq, Hkv, D, devc, stream, iters=10):
         for _ in range(3):
             o = run()
         ms = median_event_ms(run, iters, stream)
-        fl = prefill_flops(c["q_lens"], [0] * c["B"], Hq, D)
+        fl = prefill_flops(c["q_lens"], c.get("prefix_lens", [0] * c["B"]), Hq, D)
         tf = fl / (ms * 1e-3) / 1e12
         # spot check of the timed output: last token of the longest sequence, one head, direct fp32
         i = int(np.argmax(c["q_lens"]))
         a, b = int(c["qo_indptr"][i]), int(c["qo_indptr"][i + 1])
         h = Hq - 1
-        slots = c["kv_indices"][a:b].long()
+        slots = c["kv_indices"][int(c["kv_indptr"][i]):int(c["kv_indptr"][i + 1])].long()
         K, V = c["k_cache"][slots, h // (Hq // Hkv)].float(), c["v_cache"][slots, h // (Hq // Hkv)].float()
         ref = torch.softmax((K @ c["q"][b - 1, h].float()) * sm, 0) @ V
         err = float((o[b - 1, h].float() - ref).abs().max())
@@ -291,6 +314,102 @@ def bench_prefill(pkg, Hq, Hkv, D, devc, stream, iters=10):
                              "kernel": "prefill_plan_kernel + prefill_sm100_persist_kernel"})
         del ws
     return out
+
+
+def bench_store_kv(pkg, Hkv, D, devc, stream, peak, iters=20):
+    """BASELINE.md M3, slot write (replaces core/kv_cache.py:12-44): one prefill step of the bench workload (T = 142 827
+    new tokens) and one decode step at B = 256.  Algorithmic bytes: K and V rows read once and written once + 8 B of
+    slot id per token.  v is the strided view of the qkv GEMM output, as in the model (models/qwen3.py:123)."""
+    out = []
+    for T in (142827, 256):
+        n_slots = T + 4096
+        kc = torch.zeros((n_slots, Hkv, D), device=devc, dtype=torch.bfloat16)
+        vc = torch.zeros_like(kc)
+        kv = torch.randn((T, 2 * Hkv * D), device=devc, dtype=torch.bfloat16)
+        k, v = kv[:, :Hkv * D].view(T, Hkv, D), kv[:, Hkv * D:].view(T, Hkv, D)
+        slots = torch.from_numpy(np.random.default_rng(T).permutation(n_slots)[:T].astype(np.int64)).to(devc)
+        run = lambda: pkg.store_kvcache(k, v, kc, vc, slots)
+        for _ in range(3):
+            run()
+        ms = median_event_ms(run, iters, stream)
+        ok = bool(torch.equal(kc[slots], k) and torch.equal(vc[slots], v))
+        nbytes = T * (4 * Hkv * D * 2 + 8)
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        out.append({"tokens": T, "kernel_ms": ms, "algorithmic_bytes": nbytes, "gbs": gbs, "frac": gbs / peak,
+                    "bit_exact_self_check": ok, "kernel": "store_kv_rows_kernel"})
+        del kc, vc, kv, slots
+    return out
+
+
+def bench_meta(pkg, Hq, Hkv, D, devc, stream, B=256, ctx=1300, steps=50):
+    """BASELINE.md M3, metadata: a B = 256 decode step (mean context 1.3 k tokens, the bench workload's steady state)
+    through AttentionBackend.build_metadata (eager; replaces layers/attention.py:62-149) and through
+    build_metadata_for_cuda_graph_replay (the refill of the captured buffers; replaces :219-295).  host_us = wall time of
+    the call on the host (packing + launches, no sync); device_us = CUDA-event time of what it enqueued."""
+    pool = pkg.KVCachePool(torch.bfloat16, devc, B * (ctx + 2 * steps + 16) + 64, 1, Hkv, D)
+    be = pkg.AttentionBackend(pool, Hq, Hkv, D, torch.bfloat16, devc)
+    nxt = [0]
+
+    def take(n):
+        a = nxt[0]
+        nxt[0] += n
+        return list(range(a, a + n))
+    seqs = [Seq(f"m{i}", ctx, take(ctx), ctx - 1) for i in range(B)]
+    batch = Batch(pkg.ForwardMode.DECODE, seqs)
+    g = pkg.CUDAGraph()
+    be.prepare_for_cuda_graph_capture(g, B, ctx + 2 * steps + 16)
+    be.build_metadata_for_cuda_graph_capture(g, B, ctx + 2 * steps + 16)
+
+    def advance():
+        for sq in seqs:
+            sq.cached_kv_len = len(sq.kv_indices)
+            sq.token_ids.append(0)
+            sq.kv_indices.append(nxt[0])
+            nxt[0] += 1
+    res = {"batch": B, "context_len": ctx}
+    for name, fn in (("eager_build_metadata", lambda: be.build_metadata(batch)),
+                     ("graph_replay_refill", lambda: be.build_metadata_for_cuda_graph_replay(g, batch, B))):
+        host, devt = [], []
+        for i in range(steps + 5):
+            advance()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            t0 = time.perf_counter()
+            fn()
+            t1 = time.perf_counter()
+            b.record(stream)
+            b.synchronize()
+            if i >= 5:
+                host.append((t1 - t0) * 1e6)
+                devt.append(a.elapsed_time(b) * 1e3)
+        res[name] = {"host_us_median": statistics.median(host), "issue_to_done_us_median": statistics.median(devt),
+                     "h2d_bytes_per_step": int(be.slot_table.last_msg_bytes)}
+    res["full_resends_after_first_step"] = int(be.slot_table.full_resends - B)
+    return res
+
+
+def bench_decode_page1(pkg, B, L, Hq, Hkv, D, q, k_cache, v_cache, devc, stream, peak, iters=10):
+    """The headline shapes at page size 1: the only page size the reference's token-granular allocator can drive
+    (layers/attention.py:66, core/kv_cache.py:101-117).  Same pool and queries, slot-granular random page table."""
+    n = B * L
+    idx = torch.from_numpy(np.random.default_rng(1).permutation(n).astype(np.int32)).to(devc)
+    indptr = (torch.arange(B + 1, dtype=torch.int64) * L).to(torch.int32).to(devc)
+    last = torch.ones(B, dtype=torch.int32, device=devc)
+    ws = torch.empty(pkg.ops.decode_workspace_bytes(B, Hq, Hkv, D), dtype=torch.uint8, device=devc)
+    run = lambda: pkg.ops.decode(q, k_cache, v_cache, indptr, idx, last, ws, 1, D ** -0.5)
+    for _ in range(3):
+        o = run()
+    ms = median_event_ms(run, iters, stream)
+    b, h = B // 2, Hq - 1
+    sl = idx[b * L:(b + 1) * L].long()
+    K, V = k_cache[sl, h // (Hq // Hkv)].float(), v_cache[sl, h // (Hq // Hkv)].float()
+    ref = torch.softmax((K @ q[b, h].float()) * D ** -0.5, 0) @ V
+    nbytes = algorithmic_bytes(B, L, Hq, Hkv, D, 1)
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    return {"page_size": 1, "kernel_ms": ms, "algorithmic_bytes_per_launch": nbytes, "gbs": gbs, "frac": gbs / peak,
+            "frac_of_nominal_8TBs": gbs / NOMINAL_HBM_GBS, "self_check_max_abs_err": float((o[b, h].float() - ref).abs().max()),
+            "kernel": "decode_kernel + decode_merge_kernel"}
 
 
 def bench_flashinfer(B, L, ps, Hq, Hkv, D, q, k_cache, v_cache, kv_indptr, kv_indices, last_page_len, bytes_rank, devc, stream,
@@ -415,7 +534,7 @@ def run_b200_arm(args):
     pages_per_seq = -(-L // ps)
     n_pages = B * pages_per_seq
     # the e2e leg is a real decode progression (one new token per sequence per step): spare pages past the timed pool
-    grow_pages = -(-(args.steps + max(args.warmup, 3) + 4) // ps) + 1
+    grow_pages = -(-(2 * args.steps + max(args.warmup, 3) + 4) // ps) + 1      # pipelined pass + synchronised pass of the e2e leg
     num_slots = (n_pages + B * grow_pages) * ps
 
     # ---- resident state: pool (one layer), page table, inputs ---------------------------------------
@@ -555,7 +674,7 @@ def run_b200_arm(args):
     err = float((out[b_chk, h_chk].float() - ref).abs().max().item())
 
     # ---- (B) end to end through the drop-in API with host buffers -------------------------------------
-    e2e = None
+    e2e = e2e_sync = None
     if not args.no_e2e:
         be = pkg.AttentionBackend(pool, Hq, Hkv, D, torch.bfloat16, devc, page_size=ps)
         attn = pkg.Attention(Hq, D, None, Hkv, 0).to(devc)
@@ -589,7 +708,7 @@ def run_b200_arm(args):
 
         if not args.no_graph:
             e2e_graph = pkg.CUDAGraph()
-            ctx_cap = L + args.steps + max(args.warmup, 3) + 8
+            ctx_cap = L + 2 * args.steps + max(args.warmup, 3) + 8
             be.prepare_for_cuda_graph_capture(e2e_graph, B, ctx_cap)
             md0 = be.build_metadata_for_cuda_graph_capture(e2e_graph, B, ctx_cap)
             with pkg.attention_kv_cache(holder, md0):
@@ -645,6 +764,29 @@ def run_b200_arm(args):
                if e2e_graph is not None else
                "AttentionBackend.build_metadata(host Sequence lists) + Attention.forward + output read-back"}
         torch.cuda.synchronize()
+        # The same steps once more, but as the reference's decode loop runs them: the host WAITS for a step's output
+        # before it advances the sequences (core/worker.py:104 `.tolist()` every step), so packing step n+1 cannot
+        # overlap the device work of step n.  `e2e` above is the pipelined upper bound; this is the lock-step figure.
+        barrier()
+        t0 = time.perf_counter()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        for _ in range(args.steps):
+            step_e2e()
+            stream.synchronize()                 # h_out (pinned host memory) is complete: the step's result is on the host
+        s1.record(stream)
+        s1.synchronize()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([max(s0.elapsed_time(s1), wall_ms)], device=devc, dtype=torch.float64)
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sync_ms = float(t.item()) / args.steps
+        L_sync = L + e2e_steps_done[0] - args.steps / 2.0
+        e2e_sync = {"value": algorithmic_bytes(B, L_sync, Hq, Hkv, D, ps) * tp / (sync_ms * 1e-3) / 1e9, "unit": UNIT,
+                    "ms_per_step": sync_ms, "h2d_bytes_per_step": e2e["h2d_bytes_per_step"],
+                    "d2h_bytes_per_step": e2e["d2h_bytes_per_step"],
+                    "note": "host waits for each step's output before advancing the sequences (core/worker.py:104); "
+                            "max of device-event and host wall time over the K steps"}
         sl_e = torch.tensor(seqs[b_chk].kv_indices, dtype=torch.long, device=devc)
         Ke, Ve = k_cache[sl_e, h_chk // (Hq // Hkv)].float(), v_cache[sl_e, h_chk // (Hq // Hkv)].float()
         qe = d_qkv[b_chk, h_chk * D:(h_chk + 1) * D].float()
@@ -677,6 +819,15 @@ def run_b200_arm(args):
 
     # ---- (D) extra keys: prefill roofline, FlashInfer on the same inputs, the stock engine ---------------------
     prefill = gpu_ref = engine = None
+    m3 = {}
+    if rank == 0 and not args.no_m3:
+        for key, fn in (("decode_page1", lambda: bench_decode_page1(pkg, B, L, Hq, Hkv, D, q, k_cache, v_cache, devc, stream, peak)),
+                        ("store_kv", lambda: bench_store_kv(pkg, Hkv, D, devc, stream, peak)),
+                        ("meta", lambda: bench_meta(pkg, Hq, Hkv, D, devc, stream))):
+            try:
+                m3[key] = fn()
+            except Exception as e:
+                m3[key] = {"error": f"{type(e).__name__}: {e}"[:400]}
     if rank == 0 and not args.no_prefill:
         try:
             prefill = bench_prefill(pkg, Hq, Hkv, D, devc, stream)
@@ -724,7 +875,8 @@ def run_b200_arm(args):
                                       "fraction slightly above 1 is not an error",
                          "algorithmic_bytes_per_launch": bytes_rank, "frac_of_nominal_8TBs": achieved / NOMINAL_HBM_GBS},
             "prefill": prefill, "gpu_reference": gpu_ref, "engine": engine,
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk.summary(),
+            "decode_page1": m3.get("decode_page1"), "store_kv": m3.get("store_kv"), "meta": m3.get("meta"),
+            "cpu_baseline": cpu, "e2e": e2e, "e2e_sync": e2e_sync, "gpu_launches": int(launches), "clocks": clk.summary(),
             "timing": {"timed_region": timed_region,
                        "eager_ms_per_step": eager_ms_per_step, "roofline_kernel_ms_from": kernel_ms_from,
                        "eager_decode_ms_median": statistics.median(decode_ms), "paired_pass": paired},
