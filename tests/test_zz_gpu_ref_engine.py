@@ -70,3 +70,35 @@ def test_every_token_divergence_is_a_bf16_tie(engine_runs):
     if rep["cases"]:
         # b200's logits are not further from the fp32-attention logits than FlashInfer's (25 % noise allowance)
         assert rep["mean_rms_b200"] <= 1.25 * rep["mean_rms_fi"] + 1e-6, (rep["mean_rms_b200"], rep["mean_rms_fi"])
+
+
+@pytest.mark.timeout(2400)
+def test_delta_wire_and_shared_prefix_reuse_keep_every_token(engine_runs):
+    """f-2 and f-1 inside the real engine on the GPU, drop-in arm, plain argmax.
+
+    (1) ``--wire delta`` changes how a step reaches the worker (core/executor.py:86-97, core/worker_client.py:87-94), not
+        what the worker computes: its tokens must be IDENTICAL to the pickle run of the same arm, sequence by sequence.
+    (2) Config 4 through the stock scheduler: a shared-prefix workload served with admission-time prefix reuse
+        (core/scheduler.py:67-74, core/kv_cache.py:159-161) + the delta wire, twice.  The second pass is admitted
+        entirely from the radix tree.  Every request must still produce its full quota of tokens, the two passes must
+        agree on at least the first generated token of (nearly) every request (the prefix rows are re-read from other
+        slots through another code path of the prefill kernel, so later tokens may flip on bf16 ties), and nothing may
+        be left in a half-admitted state (the run ends, i.e. no sequence is lost)."""
+    delta = os.path.join(OUT, "test_ref_engine_b200_delta.json")
+    _run(["benchmarks/ref_engine.py", "--model", "0.6b", "--backend", "b200", "--num-seqs", str(NUM_SEQS), "--max-bs", "32",
+          "--argmax", "--runs", "1", "--wire", "delta", "--nccl-port", "29545", "--out", delta], timeout=900)
+    a = json.load(open(engine_runs["b200"]))["tokens"]
+    b = json.load(open(delta))["tokens"]
+    same = sum(x == y for x, y in zip(a, b))
+    assert len(a) == len(b) == NUM_SEQS and same == NUM_SEQS, f"delta wire changed tokens: {same}/{NUM_SEQS} sequences identical"
+
+    sp = os.path.join(OUT, "test_ref_engine_b200_shared_prefix.json")
+    _run(["benchmarks/ref_engine.py", "--model", "0.6b", "--backend", "b200", "--num-seqs", str(NUM_SEQS), "--max-bs", "32",
+          "--argmax", "--runs", "2", "--workload", "shared-prefix", "--prefix-len", "512", "--gen", "32", "--prefix-cache",
+          "--wire", "delta", "--nccl-port", "29547", "--out", sp], timeout=900)
+    d = json.load(open(sp))
+    assert d["cfg"]["prefix_cache"] is True and d["cfg"]["workload"] == "shared-prefix"
+    r0, r1 = d["tokens_runs"]
+    assert [len(t) for t in r0] == [32] * NUM_SEQS and [len(t) for t in r1] == [32] * NUM_SEQS
+    first_equal = sum(x[0] == y[0] for x, y in zip(r0, r1))
+    assert first_equal >= int(0.9 * NUM_SEQS), f"only {first_equal}/{NUM_SEQS} first tokens agree between the cold and the cached pass"
