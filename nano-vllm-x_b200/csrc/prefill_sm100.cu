@@ -64,9 +64,21 @@ constexpr float kLazyTau = 8.0f;
 // ---- packed f32x2 helpers (FFMA2 / FADD2 on sm_100).  The arithmetic forms are `asm volatile`: together with the
 // bar.warp.sync fences they pin the instruction ORDER of the softmax software pipeline; the mov.b64 pack / unpack forms
 // are plain register-pair aliases and cost no instruction.
+#ifndef B200_PREFILL_PACKED
+#define B200_PREFILL_PACKED 1
+#endif
+constexpr bool kPackedSoftmax = B200_PREFILL_PACKED != 0;
+#ifndef B200_PREFILL_UNIMASK
+#define B200_PREFILL_UNIMASK 1
+#endif
+constexpr bool kUnifiedMask = B200_PREFILL_UNIMASK != 0;   // masked tiles share the unmasked tile body (see softmax_tile)
 // kLeanEpilogue: output-row addresses as one 64-bit base per item + 32-bit deltas per store, 1/l scaling with packed
 // FMUL2.  On bench-shaped prompts (1..8 KV tiles per item) the epilogue was 28 % of the softmax warps' time, most of it
 // 64-bit address arithmetic of the 16 stores per thread (profiles/r2s22_tree_prefill_short_roles.txt).
+#ifndef B200_PREFILL_LEANEPI
+#define B200_PREFILL_LEANEPI 1
+#endif
+constexpr bool kLeanEpilogue = B200_PREFILL_LEANEPI != 0;
 __device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
   uint64_t r;
   asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "r"(lo), "r"(hi));
@@ -94,10 +106,15 @@ __device__ __forceinline__ uint64_t add2_ordered(uint64_t a, uint64_t b) {
 // One softmax step of one row (thread) over a 128-column S tile held in TMEM.
 // MASK is a template parameter so the (rare) masked tiles do not tax the common path with
 // predicated-off instructions (nvcc if-converts a runtime `if` around the element loop).
+template <bool MASK, int NCH = 4>
 __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t tO, const int nvalid, const bool first_pv_done,
                                              const float scale_log2, float& m_used, float& l_run, const uint32_t bar_p0,
-                                             const uint32_t bar_p1, const bool runtime_mask) {
-  uint32_t sv[4][32];
+                                             const uint32_t bar_p1, const bool runtime_mask = false) {
+  // NCH (masked tiles only, tile-uniform): number of 32-column chunks of S that hold any valid column of this
+  // query tile.  The MMA issuer trims QK to N = 32*NCH and PV to K = 32*NCH, so chunks >= NCH are neither
+  // loaded, exponentiated nor stored (their S/P columns are stale and never read).  nvalid <= 32*NCH.
+  static_assert(MASK || NCH == 4, "only masked tiles are trimmed");
+  uint32_t sv[NCH][32];
   float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
   // invalid columns -> -inf.  MASK: compile-time masked instance.  runtime_mask (kUnifiedMask): masked tiles (causal
   // diagonal, ragged sequence end) mask here and then run the SAME packed pipeline as the unmasked ones (exp2(-inf) = 0):
@@ -105,7 +122,13 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   // of the softmax warps' stalls).  The branch is tile-uniform; the warp barriers inside keep ptxas from if-converting
   // the compare / select pairs into predicated-off instructions of the common path.
   auto mask_chunks = [&](int c0, int c1) {
-    if (runtime_mask) {
+    if (MASK) {
+#pragma unroll
+      for (int c = c0; c < c1; ++c)
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+          if (c * 32 + e >= nvalid) sv[c][e] = 0xff800000u;   // -inf
+    } else if (runtime_mask) {
       sched_fence();
 #pragma unroll
       for (int c = c0; c < c1; ++c)
@@ -130,10 +153,10 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   // (loading the chunks in two halves so that the maximum of the first runs under the loads of the second was
   //  measured: -2..3 % on every shape, profiles/r2_s22_prefill_splitload_ab.txt)
 #pragma unroll
-  for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
+  for (int c = 0; c < NCH; ++c) tmem_ld_32x32b_x32(tS + c * 32, sv[c]);
   tmem_wait_ld();
-  mask_chunks(0, 4);
-  max_chunks(0, 4);
+  mask_chunks(0, NCH);
+  max_chunks(0, NCH);
   const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2;   // scale > 0: max commutes
   float alpha = 1.f;
   bool grow = false;
@@ -149,7 +172,7 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
   float s0 = 0.f, s1 = 0.f;
   // The O rescale sits AFTER the exponentials in its own (rare) branch: with the rescale ahead of them ptxas
   // hoists all 128 ex2 above it and spills 15 registers around the 32-register O chunk on the hot path.
-  {
+  if constexpr (!MASK && kPackedSoftmax) {
     // Unmasked tiles (the common case): explicit software pipeline over the 64 element PAIRS of the row in groups of
     // 4 pairs, with packed f32x2 arithmetic (FFMA2 / FADD2: half the FMA-pipe instructions of the scalar form).
     // Per group two instruction queues are interleaved one to one:
@@ -209,6 +232,63 @@ __device__ __forceinline__ void softmax_tile(const uint32_t tS, const uint32_t t
       s0 = __uint_as_float(lo);
       s1 = __uint_as_float(hi);
     }
+  } else if constexpr (!MASK) {
+    // Unmasked tiles (the common case): explicit software pipeline over the 128 elements.  The scale FMA runs
+    // kAhead elements ahead of its MUFU.EX2, the row-sum add and the bf16 pack kAhead elements behind it, so every
+    // MUFU (one per 8 clk per scheduler) has independent FMA-pipe work beside it.
+    constexpr int kAhead = 12;
+    uint32_t pw[64];
+#pragma unroll
+    for (int e = 0; e < kAhead; ++e)
+      sv[e >> 5][e & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[e >> 5][e & 31]), scale_log2, neg_m));
+#pragma unroll
+    for (int e = 0; e < 128 + kAhead; ++e) {
+      if ((e & 7) == 0) sched_fence();
+      if (e < 128) sv[e >> 5][e & 31] = __float_as_uint(exp2_ordered(__uint_as_float(sv[e >> 5][e & 31])));
+      if (e + kAhead < 128) {
+        const int f = e + kAhead;
+        sv[f >> 5][f & 31] = __float_as_uint(fma_ordered(__uint_as_float(sv[f >> 5][f & 31]), scale_log2, neg_m));
+      }
+      if (e >= kAhead) {
+        const int d = e - kAhead;
+        if (d & 1) {
+          s1 = add_ordered(s1, __uint_as_float(sv[d >> 5][d & 31]));
+          pw[d >> 1] = pack_bf16x2_ordered(__uint_as_float(sv[(d - 1) >> 5][(d - 1) & 31]), __uint_as_float(sv[d >> 5][d & 31]));
+          if ((d & 31) == 31) {
+            const int c = d >> 5;
+            tmem_st_32x32b_x16(tS + c * 16, *reinterpret_cast<uint32_t(*)[16]>(&pw[c * 16]));   // P: packed bf16x2 over S
+            if (!rescale && (c == 1 || c == 3)) {     // hand P over in two halves: PV starts on the first
+              tmem_wait_st();
+              tc_fence_before();
+              mbar_arrive(c == 1 ? bar_p0 : bar_p1);
+            }
+          }
+        } else {
+          s0 = add_ordered(s0, __uint_as_float(sv[d >> 5][d & 31]));
+        }
+      }
+    }
+  } else {
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    uint32_t pw[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      const float a = exp2_fma(__uint_as_float(sv[c][2 * e]), scale_log2, neg_m);
+      const float b = exp2_fma(__uint_as_float(sv[c][2 * e + 1]), scale_log2, neg_m);
+      s0 += a;
+      s1 += b;
+      pw[e] = pack_bf16x2(a, b);
+    }
+    tmem_st_32x32b_x16(tS + c * 16, pw);            // P: 64 packed bf16x2 columns over S
+    constexpr int kFirst = NCH > 1 ? 1 : 0;         // hand P over in two halves: PV starts on the first
+    if (!rescale && (c == kFirst || c == NCH - 1)) { // while the second is still in the exp unit
+      tmem_wait_st();
+      tc_fence_before();
+      if (c == kFirst) mbar_arrive(bar_p0);
+      if (c == NCH - 1) mbar_arrive(bar_p1);
+    }
+  }
   }
   if (rescale) {                                    // O must carry the new scale before PV(j) accumulates into it
 #pragma unroll
@@ -343,8 +423,17 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
   const int G = 1 << log2_g;
   const int tok_per_tile = kTM >> log2_g;
   const int tok_per_cta = 2 * tok_per_tile;
-  // (Trimming QK / softmax / PV of partly valid last tiles to 32-column chunks, an unstaged epilogue and a 64-bit-address
-  //  epilogue were measured and lost: profiles/r1_s38_prefill_flags_ab.txt; they live in git history.)
+  // Trimmed last tiles: 32-column chunks of KV tile j that hold columns below the query tile's kv_hi.  Bench-shaped
+  // prompts (100..1024 tokens) own 1..8 KV tiles per item and the last one of each query tile is only
+  // partly valid (causal diagonal of a 32/64-token packed tile, ragged sequence end): QK, softmax and PV
+  // run on 32*nch columns instead of 128 (8-12 % of all chunk steps on the bench prompts).
+  // Compile-time switches, set from a same-box A/B on B200 of a build that had them as run-time flags
+  // (profiles/r1_s38_prefill_flags_ab.txt; bench prompts Hq32 / uniform 16x4096 Hq32, fraction of bf16 peak):
+  //   none 0.303 / 0.633   trim 0.298 / 0.640   staged 0.319 / 0.650   lean_q 0.326 / 0.648   all three 0.291 / 0.670
+  // Trimming costs more than it saves on short prompts (four masked-softmax instances; the kernel is ~7000 SASS
+  // instructions and every extra hot path shows), so it stays off; dead branches are removed by the compiler.
+  constexpr bool trim = false, staged = true, lean_q = true;
+  auto chunks_of = [&](int kv_hi, int j) { return trim ? min(4, (kv_hi - j * kTN + 31) >> 5) : 4; };
 
   const uint32_t smem = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = smem_u32(&s_bar[0]);
@@ -653,8 +742,8 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       mbar_wait(bar_q, qn & 1);
       mbar_wait(bar_full(base % kRing), (base / kRing) & 1);
       tc_fence_after();
-      if (g.nt0 > 0) issue_qk(0, base, 4);
-      if (g.nt1 > 0) issue_qk(1, base, 4);
+      if (g.nt0 > 0) issue_qk(0, base, chunks_of(g.kvhi0, 0));
+      if (g.nt1 > 0) issue_qk(1, base, chunks_of(g.kvhi1, 0));
       umma_commit_elect(bar_empty(base % kRing));                        // K(0) free once both QK(0) are done
       if (g.J == 1) umma_commit_elect(bar_qfree);                        // last QK of the item: Q may be refilled
       for (int j = 0; j < g.J; ++j) {
@@ -666,7 +755,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           const int ntt = t ? g.nt1 : g.nt0;
           const int kvhit = t ? g.kvhi1 : g.kvhi0;
           if (j < ntt) {
-            const int nks = 2 * 4;
+            const int nks = 2 * chunks_of(kvhit, j);
             mbar_wait(bar_p(t, 0), pc[t] & 1);                           // first 64 columns of P_t(j) are in TMEM
             tc_fence_after();
             issue_pv(t, fv, 0, j > 0, nks);
@@ -682,7 +771,7 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
               tc_fence_after();
               k_ready = true;
             }
-            issue_qk(t, fk, 4);
+            issue_qk(t, fk, chunks_of(kvhit, j + 1));
           }
         }
         umma_commit_elect(bar_empty(fv % kRing));
@@ -718,7 +807,13 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
         const int kv0 = j * kTN;
         const bool need_mask = (kv0 + kTN - 1 > lim0) || (kv0 + kTN > kv_hi);
         const int nvalid = need_mask ? min(lim, kv_hi - 1) - kv0 + 1 : kTN;   // valid columns of my row in this tile
-        softmax_tile(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), need_mask);
+        if constexpr (kUnifiedMask) {
+          softmax_tile<false>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1), need_mask);
+        } else if (need_mask) {
+          softmax_tile<true, 4>(tS, tO, nvalid, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
+        } else {
+          softmax_tile<false>(tS, tO, kTN, j > 0, p.scale_log2, m_used, l_run, bar_p(t, 0), bar_p(t, 1));
+        }
       }
       // ---- epilogue -------------------------------------------------------------------------------------------
       const bool has = ntt > 0;
@@ -736,17 +831,40 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
       const uint32_t stage = smem + kWsOffStage + (uint32_t)warp * 4096u;
       const int rows_ok = tokst << log2_g;
       const int rsub = lane >> 3, piece = lane & 7;
-      if (!has) {
+      if (!has || !staged) {
         // thread = row, straight from the TMEM layout.  Rows without any visible KV (Lkv == 0, or causal with
-        // Lkv < Lq) are zeros.
+        // Lkv < Lq) are zeros; with data this is the unstaged form kept for A/B measurements.
         if (r < rows_ok) {
           uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + my_tok) * p.out_row_stride +
                                                 (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+          if (!has) {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
+            for (int e = 0; e < 16; ++e) dst[e] = make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+        if (has) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (int64_t)(d.q0 + (r < rows_ok ? my_tok : d.j0)) * p.out_row_stride +
+                                                (int64_t)(d.kvh * G + (r & (G - 1))) * kTD);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t ov[32];
+            tmem_ld_32x32b_x32(tO + c * 32, ov);
+            tmem_wait_ld();
+            if (r < rows_ok) {
+#pragma unroll
+              for (int j8 = 0; j8 < 4; ++j8) {
+                uint4 w;
+                w.x = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+                w.y = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+                w.z = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+                w.w = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+                dst[c * 4 + j8] = w;
+              }
+            }
+          }
         }
       }
-      if (has) {
+      if (kLeanEpilogue && has && staged) {
         // one 64-bit base per item (first token of this query tile, first head of the KV head's group, this lane's
         // 16-byte piece); per store a 32-bit element delta from the packed row index R = (token, head-in-group)
         __nv_bfloat16* const out0 = p.out + (int64_t)(d.q0 + d.j0 + t * tok_per_tile) * p.out_row_stride +
@@ -789,6 +907,40 @@ __global__ void __launch_bounds__(kWsThreads, 1) prefill_sm100_persist_kernel(co
           }
           __syncwarp();                                    // the next half (or item) overwrites the staging rows
         }
+      }
+#pragma unroll
+      for (int half = 0; half < 2 && has && staged && !kLeanEpilogue; ++half) {
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          uint32_t ov[32];
+          tmem_ld_32x32b_x32(tO + (half * 2 + cc) * 32, ov);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j8 = 0; j8 < 4; ++j8) {
+            const uint32_t w0 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 0]) * inv_l, __uint_as_float(ov[j8 * 8 + 1]) * inv_l);
+            const uint32_t w1 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 2]) * inv_l, __uint_as_float(ov[j8 * 8 + 3]) * inv_l);
+            const uint32_t w2 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 4]) * inv_l, __uint_as_float(ov[j8 * 8 + 5]) * inv_l);
+            const uint32_t w3 = pack_bf16x2(__uint_as_float(ov[j8 * 8 + 6]) * inv_l, __uint_as_float(ov[j8 * 8 + 7]) * inv_l);
+            const uint32_t dst_s = stage + (uint32_t)lane * 128u + (uint32_t)(((cc * 4 + j8) ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};\n" ::"r"(dst_s), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int row = 4 * k + rsub;                  // row of this warp's 32
+          uint4 w;
+          const uint32_t src_s = stage + (uint32_t)row * 128u + (uint32_t)((piece ^ (row & 7)) << 4);
+          asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];\n" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(src_s) : "memory");
+          const int R = (warp & 3) * 32 + row;           // packed row of tile t
+          if (R < rows_ok) {
+            const int tok = d.j0 + t * tok_per_tile + (R >> log2_g);
+            __nv_bfloat16* dst = p.out + (int64_t)(d.q0 + tok) * p.out_row_stride +
+                                 (int64_t)(d.kvh * G + (R & (G - 1))) * kTD + half * 64 + piece * 8;
+            *reinterpret_cast<uint4*>(dst) = w;
+          }
+        }
+        __syncwarp();                                    // the next half (or item) overwrites the staging rows
       }
       tc_fence_before();   // O_t reads are complete before this group's next P arrive lets PV_t(0) overwrite O_t
     }
